@@ -1,0 +1,64 @@
+/* vpt_host.h — C entry points of the host library (libvpt_host.so) for callers
+ * without a C++ toolchain (the Python tests / bench drive the renderer through
+ * these with ctypes). They wrap the C++ facade of
+ * volumetric-path-tracer_b200/host/vpt_pathtrace.h, which in turn reaches the
+ * GPU only through include/vpt_cuda.h. Host-only queries (bvh, lights, state
+ * seeds) run without a GPU; everything that renders needs one.
+ *
+ * Reference call sequence mirrored: run_offline
+ * (apps/ypathtrace/ypathtrace.cpp:41-87): load_scene -> make_bvh -> make_lights
+ * -> make_state -> pathtrace_samples xN -> get_render.
+ */
+#ifndef VPT_HOST_H
+#define VPT_HOST_H
+
+#include "vpt_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vpth_scene  vpth_scene;  /* scene_data + bvh_scene + pathtrace_lights */
+typedef struct vpth_render vpth_render; /* pathtrace_params + pathtrace_state */
+
+const char* vpth_last_error(void);
+
+/* load_scene + make_bvh + make_lights (host only) */
+int  vpth_load_scene(const char* path, vpth_scene** out);
+void vpth_free_scene(vpth_scene* scene);
+/* counts: cameras, instances, shapes, materials, textures, environments,
+ * volumes, vol_instances, sdfs, lights, scene bvh nodes, total shape bvh nodes */
+int  vpth_scene_counts(const vpth_scene* scene, int32_t counts[12]);
+
+/* host-built structures, for comparison with the reference's */
+int  vpth_bvh_size(const vpth_scene* scene, int shape, int32_t* num_nodes, int32_t* num_prims);
+int  vpth_bvh_copy(const vpth_scene* scene, int shape, vpt_bvh_node* nodes, int32_t* prims);
+int  vpth_light_info(const vpth_scene* scene, int light, int32_t ids[3], int32_t* cdf_size);
+int  vpth_light_cdf(const vpth_scene* scene, int light, float* cdf);
+
+/* make_state; rngs_out (optional) receives the initial per-pixel generators */
+int  vpth_render_create(vpth_scene* scene, const vpt_params* params, vpth_render** out);
+void vpth_render_free(vpth_render* render);
+int  vpth_render_size(const vpth_render* render, int32_t* width, int32_t* height);
+int  vpth_render_get_rngs(vpth_render* render, uint64_t* rngs); /* [w*h][2], synced from the device */
+/* back to sample 0 with the make_state generators, advanced by rng_offset draws per pixel */
+int  vpth_render_reset(vpth_render* render, uint64_t rng_offset);
+
+/* pathtrace_samples with a batch of nsamples; blocking */
+int  vpth_render_samples(vpth_render* render, int nsamples);
+int  vpth_render_done_samples(const vpth_render* render);
+/* normalized != 0: get_render (sum / samples); else the raw sums */
+int  vpth_render_get_image(vpth_render* render, float* rgba, int normalized);
+int  vpth_render_stats(const vpth_render* render, vpt_trace_stats* stats);
+/* device pointer of the accumulation image (for a collective), or null */
+void* vpth_render_device_image(vpth_render* render);
+
+int  vpth_intersect(vpth_scene* scene, const float* rays, int n, int instance, int32_t* ids,
+         float* uvd);
+int  vpth_spheretrace(vpth_scene* scene, const float* rays, int n, int maxiter, int32_t* ids,
+         float* dn);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VPT_HOST_H */

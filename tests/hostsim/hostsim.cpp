@@ -1,0 +1,164 @@
+// hostsim — TEST-ONLY debugging aid. Compiles the device headers
+// (volumetric-path-tracer_b200/csrc/*.cuh) for the host CPU and runs them one
+// pixel at a time, so that the CUDA code's logic can be single-stepped against
+// the reference (oracle/_ref/ref_render) on a box without a GPU. With the host
+// libm the stochastic shaders replay the reference's random streams exactly,
+// which localises any divergence to a line of code.
+//
+// It is NOT part of the product: nothing under volumetric-path-tracer_b200/
+// builds, links or calls this, and the shipped libraries have no CPU path.
+//
+// usage: hostsim <scene.vptscene> <out.vptarch> [--shader NAME] [--samples N]
+//        [--resolution R] [--bounces B] [--noimplicitmis] [--stmaxiter M]
+//        [--rays rays.vptarch] [--instance K] [--threads T]
+#define VPT_HOST_POOL 1
+#include <chrono>
+#include <thread>
+
+#include "../../volumetric-path-tracer_b200/csrc/shaders.cuh"
+#include "../../volumetric-path-tracer_b200/csrc/upload.cuh"
+#include "../../volumetric-path-tracer_b200/host/vpt_archive.h"
+#include "../../volumetric-path-tracer_b200/host/vpt_pathtrace.h"
+
+using namespace vpt;
+
+template <int S>
+static void render_rows(const DScene& sc, const DParams& prm, pathtrace_state& state, int nsamples,
+    int tid, int nthreads) {
+  int  stack_mem[vpt_stack_depth];
+  auto st = stack_t{stack_mem, 1};
+  for (int idx = tid; idx < state.width * state.height; idx += nthreads) {
+    auto rng = rng_t{state.rngs[idx].state, state.rngs[idx].inc};
+    auto acc = state.image[idx];
+    for (int s = 0; s < nsamples; s++) {
+      auto ray = sample_camera(sc, prm, idx, rng);
+      auto rad = guard_radiance(shade_path<S>(sc, prm, ray, rng, st));
+      acc      = acc + rad;
+    }
+    state.image[idx] = acc;
+    state.rngs[idx]  = {rng.state, rng.inc};
+  }
+}
+
+template <int S>
+static void render(const DScene& sc, const DParams& prm, pathtrace_state& state, int nsamples,
+    int nthreads) {
+  auto threads = std::vector<std::thread>{};
+  for (int t = 0; t < nthreads; t++)
+    threads.emplace_back([&, t] { render_rows<S>(sc, prm, state, nsamples, t, nthreads); });
+  for (auto& t : threads) t.join();
+}
+
+int main(int argc, const char** argv) {
+  if (argc < 3) {
+    fprintf(stderr, "usage: hostsim scene.vptscene out.vptarch [opts]\n");
+    return 2;
+  }
+  auto params    = pathtrace_params{};
+  auto rays_file = std::string{};
+  auto instance  = -1;
+  auto nthreads  = (int)std::max(1u, std::thread::hardware_concurrency());
+  for (int i = 3; i < argc; i++) {
+    auto a    = std::string{argv[i]};
+    auto next = [&]() -> std::string { return i + 1 < argc ? argv[++i] : ""; };
+    if (a == "--shader") {
+      auto name = next();
+      for (size_t k = 0; k < pathtrace_shader_names.size(); k++)
+        if (pathtrace_shader_names[k] == name) params.shader = (pathtrace_shader_type)k;
+    } else if (a == "--samples") params.samples = std::stoi(next());
+    else if (a == "--resolution") params.resolution = std::stoi(next());
+    else if (a == "--bounces") params.bounces = std::stoi(next());
+    else if (a == "--stmaxiter") params.spheretrace_maxiter = std::stoi(next());
+    else if (a == "--noimplicitmis") params.noimplicit_mis = true;
+    else if (a == "--rays") rays_file = next();
+    else if (a == "--instance") instance = std::stoi(next());
+    else if (a == "--threads") nthreads = std::stoi(next());
+  }
+  auto error = std::string{};
+  auto scene = scene_data{};
+  if (!load_scene(argv[1], scene, error)) {
+    fprintf(stderr, "hostsim: %s\n", error.c_str());
+    return 1;
+  }
+  auto bvh     = make_bvh(scene, params);
+  auto lights  = make_lights(scene, params);
+  auto storage = scene_desc_storage{};
+  make_scene_desc(storage, scene, bvh, lights);
+  auto flat = flat_scene{};
+  if (flatten_scene(storage.desc, flat, error) != VPT_OK) {
+    fprintf(stderr, "hostsim: %s\n", error.c_str());
+    return 1;
+  }
+  auto& sc  = flat.d;
+  auto  out = archive{};
+  if (!rays_file.empty()) {
+    auto ra = archive{};
+    if (!ra.load(rays_file, error)) return 1;
+    auto rays = ra.find("rays");
+    auto n    = (size_t)rays->dims[0];
+    auto ids  = std::vector<int>(n * 3);
+    auto fl   = std::vector<float>(n * 3);
+    auto sid  = std::vector<int>(n * 3);
+    auto sfl  = std::vector<float>(n * 4);
+    int  stack_mem[vpt_stack_depth];
+    auto st      = stack_t{stack_mem, 1};
+    auto has_sdf = sc.num_sdfs + sc.num_vol_instances > 0;
+    for (size_t i = 0; i < n; i++) {
+      auto p   = rays->f32() + i * 8;
+      auto ray = ray3{{p[0], p[1], p[2]}, {p[3], p[4], p[5]}, p[6], p[7]};
+      auto h   = instance >= 0 ? intersect_instance(sc, instance, ray, st)
+                               : intersect_scene(sc, ray, st);
+      ids[i * 3 + 0] = h.hit, ids[i * 3 + 1] = h.hit ? h.instance : -1;
+      ids[i * 3 + 2] = h.hit ? h.element : -1;
+      fl[i * 3 + 0] = h.hit ? h.uv.x : 0, fl[i * 3 + 1] = h.hit ? h.uv.y : 0;
+      fl[i * 3 + 2] = h.hit ? h.distance : 0;
+      if (has_sdf) {
+        auto r   = spheretrace(sc, ray, params.spheretrace_maxiter);
+        auto nrm = f3{0, 0, 0};
+        if (r.hit) {
+          auto pos = ray_point(ray, r.dist);
+          nrm = r.instance != invalidid
+                    ? eval_sdf_normal_grid(sc, ld_vol_instance(sc, r.instance), pos, r.dist)
+                    : eval_sdf_normal_fn(ld_sdf(sc, r.sdf), pos, r.dist);
+        }
+        sid[i * 3 + 0] = r.hit, sid[i * 3 + 1] = r.hit ? r.instance : -1;
+        sid[i * 3 + 2] = r.hit ? r.sdf : -1;
+        sfl[i * 4 + 0] = r.hit ? r.dist : 0;
+        sfl[i * 4 + 1] = nrm.x, sfl[i * 4 + 2] = nrm.y, sfl[i * 4 + 3] = nrm.z;
+      }
+    }
+    out.add_i32("hits.ids", {n, 3}, ids.data());
+    out.add_f32("hits.f", {n, 3}, fl.data());
+    if (has_sdf) {
+      out.add_i32("sdfhits.ids", {n, 3}, sid.data());
+      out.add_f32("sdfhits.f", {n, 4}, sfl.data());
+    }
+  } else {
+    auto state = make_state(scene, params);
+    auto prm   = DParams{params.camera, (int)params.shader, params.samples, params.bounces,
+        params.noimplicit_mis ? 1 : 0, params.spheretrace_maxiter, state.width, state.height};
+    auto t0 = std::chrono::steady_clock::now();
+    switch ((int)params.shader) {
+      case 0: render<0>(sc, prm, state, params.samples, nthreads); break;
+      case 1: render<1>(sc, prm, state, params.samples, nthreads); break;
+      case 2: render<2>(sc, prm, state, params.samples, nthreads); break;
+      case 3: render<3>(sc, prm, state, params.samples, nthreads); break;
+      case 4: render<4>(sc, prm, state, params.samples, nthreads); break;
+      case 5: render<5>(sc, prm, state, params.samples, nthreads); break;
+      case 6: render<6>(sc, prm, state, params.samples, nthreads); break;
+      case 7: render<7>(sc, prm, state, params.samples, nthreads); break;
+      default: render<8>(sc, prm, state, params.samples, nthreads); break;
+    }
+    auto seconds = (float)std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    out.add_f32("image_sum", {(uint64_t)state.height, (uint64_t)state.width, 4},
+        (const float*)state.image.data());
+    out.add("rngs_after", dt_u64, {(uint64_t)state.rngs.size(), 2}, state.rngs.data());
+    int meta[4] = {state.width, state.height, params.samples, nthreads};
+    out.add_i32("meta", {4}, meta);
+    out.add_f32("seconds", {1}, &seconds);
+    printf("hostsim: %dx%d %d spp shader=%s %.3f s\n", state.width, state.height, params.samples,
+        pathtrace_shader_names[(int)params.shader].c_str(), seconds);
+  }
+  if (!out.save(argv[2], error)) return 1;
+  return 0;
+}

@@ -1,0 +1,131 @@
+// dscene.cuh — the flattened scene as it lies in HBM, and the load helpers.
+//
+// Everything a path touches is a 16-byte-aligned record read with 128-bit
+// loads through the read-only path:
+//   nodes      2 x f4 per BVH node: {min.xyz, max.x} {max.y, max.z, start, meta}
+//              meta = num | axis << 16 | internal << 24. All shape BVHs and the
+//              scene BVH are concatenated; `start` is rebased at upload so an
+//              internal node points at its first child in this array and a
+//              leaf at its first primitive record (f4 index) / scene_prims slot.
+//   prims      primitives gathered in BVH leaf order, vertex positions inline:
+//              quad = 4 x f4 {p_k.xyz, payload}, triangle = 3 x f4;
+//              payload of the first f4 = element index.
+//   inst_trav  4 x f4 per instance: columns of inverse(frame, non_rigid) in xyz;
+//              w = {shape root node, shape kind, shape id, material id}
+//   inst_frame 4 x f4 per instance: forward frame columns.
+// The reference layout this replaces: bvh_data / shape_data / instance_data
+// (yocto_bvh.h:73-92, yocto_shape.h:74, yocto_scene.h:142-148).
+#pragma once
+
+#include "vmath.cuh"
+
+namespace vpt {
+
+enum shape_kind : int { kind_empty = 0, kind_triangles = 1, kind_quads = 2 };
+
+struct DScene {
+  // acceleration
+  const f4*  nodes;
+  const f4*  prims;
+  const int* scene_prims;
+  const f4*  inst_trav;
+  const f4*  inst_frame;
+  int        scene_root;  // node index of the scene BVH root, -1 if none
+  int        num_instances;
+  // shapes for shading: 2 x i4 per shape {kind, pos, nrm, tex} {col, elem, 0, 0}
+  const i4*    shapes;
+  const float* vpos;   // 3 floats per vertex
+  const float* vnrm;   // 3 floats per vertex
+  const float* vtex;   // 2 floats per vertex
+  const f4*    vcol;   // 4 floats per vertex
+  const i4*    elems;  // vertex indices per element (triangles: w = -1)
+  // materials: 6 x f4 per material
+  const f4* materials;
+  // textures: i4 {w, h, flags(bit0 linear, bit1 float), offset} ; texel pools
+  const i4*            textures;
+  const unsigned char* texb;  // 4 bytes per texel
+  const f4*            texf;
+  const float*         srgb_lut;  // 256 entries: srgb_to_rgb(b / 255.0f), host glibc
+  // cameras: 5 x f4 per camera
+  const f4* cameras;
+  // environments: 9 x f4 per env: frame(4) inverse rigid frame(4) {emission, tex}
+  const f4* environments;
+  int       num_environments;
+  // lights: 2 x i4 per light {instance, environment, sdf, cdf_off} {cdf_n,0,0,0}
+  const i4*    lights;
+  const float* cdf;
+  int          num_lights;
+  // sdf grids / functions
+  const f4*    vol_instances;  // 4 x f4: frame cols; w = {scalef, volume, material, 0}
+  const f4*    volumes;        // 2 x f4: {w, h, d (ints), res} {offset (int), 0, 0, 0}
+  const float* voxels;
+  const f4*    sdfs;  // 10 x f4: frame(4; w = type, material), inverse rigid (4), params, whd
+  int          num_vol_instances;
+  int          num_sdfs;
+};
+
+struct DParams {
+  int camera;
+  int shader;
+  int samples;   // total target (samples == 1 -> preview branch)
+  int bounces;
+  int noimplicit_mis;
+  int spheretrace_maxiter;
+  int width, height;
+};
+
+// ---- loads -----------------------------------------------------------------
+VPT_FN f4 ld4(const f4* p) {
+#if defined(__CUDA_ARCH__)
+  auto v = __ldg(reinterpret_cast<const float4*>(p));
+  return {v.x, v.y, v.z, v.w};
+#else
+  return *p;
+#endif
+}
+VPT_FN i4 ld4(const i4* p) {
+#if defined(__CUDA_ARCH__)
+  auto v = __ldg(reinterpret_cast<const int4*>(p));
+  return {v.x, v.y, v.z, v.w};
+#else
+  return *p;
+#endif
+}
+VPT_FN float ld1(const float* p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+VPT_FN int ld1(const int* p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+VPT_FN f3 ld3(const float* p) { return {ld1(p), ld1(p + 1), ld1(p + 2)}; }
+VPT_FN f2 ld2(const float* p) { return {ld1(p), ld1(p + 1)}; }
+
+VPT_FN frame3 ld_frame(const f4* p) {
+  auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), d = ld4(p + 3);
+  return {xyz(a), xyz(b), xyz(c), xyz(d)};
+}
+
+// ---- ray / hit -------------------------------------------------------------
+struct ray3 {
+  f3    o, d;
+  float tmin, tmax;
+};
+VPT_FN ray3 make_ray(f3 o, f3 d) { return {o, d, 1e-4f, flt_max}; }  // yocto_geometry.h:118-133
+VPT_FN f3 ray_point(const ray3& r, float t) { return r.o + r.d * t; }
+
+struct hit_t {
+  int   instance, element;
+  f2    uv;
+  float distance;
+  bool  hit;
+};
+
+}  // namespace vpt

@@ -1,0 +1,129 @@
+// lights.cuh — light direction sampling and its solid-angle pdf.
+// Restates sample_lights / sample_lights_pdf (yocto_pathtrace.cpp:312-421) and
+// the discrete-CDF helpers of yocto_sampling.h:368-395. There is no shadow ray
+// in this renderer: sampling only picks a direction; the pdf re-intersects each
+// mesh light's instance up to 100 times along that direction (instance-targeted
+// traversals), marches the analytic sdf of each sdf light, and looks up the
+// environment texel probability.
+#pragma once
+
+#include "bsdf.cuh"
+#include "bvh.cuh"
+#include "sdf.cuh"
+
+namespace vpt {
+
+// sample_discrete: clamp then std::upper_bound (same bisection as libstdc++)
+VPT_FN int sample_discrete(const float* cdf, int n, float r) {
+  auto last = ld1(cdf + n - 1);
+  r         = vclamp(r * last, (float)0, last - (float)0.00001);
+  int first = 0, len = n;
+  while (len > 0) {
+    auto half = len >> 1;
+    auto mid  = first + half;
+    if (r < ld1(cdf + mid)) {
+      len = half;
+    } else {
+      first = mid + 1;
+      len   = len - half - 1;
+    }
+  }
+  return vclamp(first, 0, n - 1);
+}
+VPT_FN float sample_discrete_pdf(const float* cdf, int idx) {
+  if (idx == 0) return ld1(cdf);
+  return ld1(cdf + idx) - ld1(cdf + idx - 1);
+}
+VPT_FN int sample_uniform(int size, float r) { return vclamp((int)(r * size), 0, size - 1); }
+
+// sample_lights (yocto_pathtrace.cpp:312-350)
+VPT_FN f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2 ruv) {
+  auto light_id = sample_uniform(sc.num_lights, rl);
+  auto l0 = ld4(sc.lights + 2 * light_id), l1 = ld4(sc.lights + 2 * light_id + 1);
+  if (l0.x != invalidid) {
+    auto in      = ld_instance(sc, l0.x);
+    auto element = sample_discrete(sc.cdf + l0.w, l1.x, rel);
+    auto uv      = ruv;
+    if (in.s.kind == kind_triangles) {
+      auto sq = vsqrt(ruv.x);
+      uv      = {1 - sq, ruv.y * sq};
+    }
+    auto lposition = eval_position(sc, in, element, uv);
+    return normalize(lposition - position);
+  } else if (l0.z != invalidid) {
+    auto p       = sc.sdfs + 10 * l0.z;
+    auto inv     = ld_frame(p + 4);  // inverse(sdf.frame), rigid, host-precomputed
+    auto whd     = xyz(ld4(p + 9));
+    auto wlightp = transform_point(inv, f3{ruv.x, ruv.y, 1} * whd);
+    return normalize(wlightp - position);
+  } else if (l0.y != invalidid) {
+    auto e  = sc.environments + 9 * l0.y;
+    auto em = ld4(e + 8);
+    if (f2i(em.w) != invalidid) {
+      auto tex = ld4(sc.textures + f2i(em.w));
+      auto idx = sample_discrete(sc.cdf + l0.w, l1.x, rel);
+      auto uv  = f2{((idx % tex.x) + 0.5f) / tex.x, ((idx / tex.x) + 0.5f) / tex.y};
+      return transform_direction(ld_frame(e),
+          f3{vcos(uv.x * 2 * pif) * vsin(uv.y * pif), vcos(uv.y * pif),
+              vsin(uv.x * 2 * pif) * vsin(uv.y * pif)});
+    } else {
+      return sample_sphere(ruv);
+    }
+  }
+  return {0, 0, 0};
+}
+
+// sample_lights_pdf (yocto_pathtrace.cpp:353-421)
+VPT_FN float sample_lights_pdf(const DScene& sc, f3 position, f3 direction,
+    int spheretrace_maxiter, stack_t st, unsigned long long* ray_counter = nullptr) {
+  auto pdf = 0.0f;
+  for (auto li = 0; li < sc.num_lights; li++) {
+    auto l0 = ld4(sc.lights + 2 * li), l1 = ld4(sc.lights + 2 * li + 1);
+    if (l0.x != invalidid) {
+      auto in            = ld_instance(sc, l0.x);
+      auto area          = ld1(sc.cdf + l0.w + l1.x - 1);
+      auto lpdf          = 0.0f;
+      auto next_position = position;
+      for (auto bounce = 0; bounce < 100; bounce++) {
+        auto isec = intersect_instance(sc, l0.x, make_ray(next_position, direction), st);
+        if (ray_counter) (*ray_counter)++;
+        if (!isec.hit) break;
+        auto lposition = eval_position(sc, in, isec.element, isec.uv);
+        auto lnormal   = eval_element_normal(sc, in, isec.element);
+        lpdf += distance_squared(lposition, position) / (vabs(dot(lnormal, direction)) * area);
+        next_position = lposition + direction * 1e-3f;
+      }
+      pdf += lpdf;
+    } else if (l0.z != invalidid) {
+      auto ray  = make_ray(position, direction);
+      auto isec = spheretrace_one(sc, ray, l0.z, spheretrace_maxiter);
+      if (isec.hit) {
+        auto lposition = ray_point(ray, isec.dist);
+        // the reference evaluates the normal at the shading position (quirk kept)
+        auto lnormal = eval_sdf_normal_fn(ld_sdf(sc, isec.sdf), position, isec.dist);
+        auto area    = ld1(sc.cdf + l0.w + l1.x - 1);
+        pdf += distance_squared(lposition, position) / (vabs(dot(lnormal, direction)) * area);
+      }
+    } else if (l0.y != invalidid) {
+      auto e  = sc.environments + 9 * l0.y;
+      auto em = ld4(e + 8);
+      if (f2i(em.w) != invalidid) {
+        auto tex      = ld4(sc.textures + f2i(em.w));
+        auto wl       = transform_direction(ld_frame(e + 4), direction);
+        auto texcoord = environment_texcoord(wl);
+        auto i    = vclamp((int)(texcoord.x * tex.x), 0, tex.x - 1);
+        auto j    = vclamp((int)(texcoord.y * tex.y), 0, tex.y - 1);
+        auto prob = sample_discrete_pdf(sc.cdf + l0.w, j * tex.x + i) /
+                    ld1(sc.cdf + l0.w + l1.x - 1);
+        auto angle = (2 * pif / tex.x) * (pif / tex.y) * vsin(pif * (j + 0.5f) / tex.y);
+        pdf += prob / angle;
+      } else {
+        pdf += 1 / (4 * pif);
+      }
+    }
+  }
+  pdf *= (float)1 / (float)sc.num_lights;
+  return pdf;
+}
+
+}  // namespace vpt

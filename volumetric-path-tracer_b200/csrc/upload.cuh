@@ -1,0 +1,390 @@
+// upload.cuh — host side of vpt_cuda_upload_scene: validates a vpt_scene_desc
+// and flattens it into the 16-byte-aligned HBM layout of dscene.cuh.
+// Host-only code (runs once per scene); nothing here is on the per-path route.
+#pragma once
+
+#if defined(VPT_HOST_POOL)
+// tests/hostsim only: keep the flattened arrays in host memory
+#include <cstdlib>
+typedef int cudaError_t;
+enum { cudaSuccess = 0, cudaErrorMemoryAllocation = 2 };
+inline const char* cudaGetErrorString(cudaError_t) { return "host pool error"; }
+#else
+#include <cuda_runtime.h>
+#endif
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vpt_cuda.h"
+#include "bvh.cuh"
+#include "dscene.cuh"
+
+namespace vpt {
+
+struct device_pool {
+  std::vector<void*> blocks;
+  size_t             bytes = 0;
+  template <typename T>
+  cudaError_t upload(const std::vector<T>& host, const T** out) {
+    *out = nullptr;
+    // keep every pool non-null so kernels may form (never dereference) pointers
+    auto n = host.size() * sizeof(T);
+#if defined(VPT_HOST_POOL)
+    void* d = aligned_alloc(256, ((n ? n : 16) + 255) / 256 * 256);
+    if (!d) return cudaErrorMemoryAllocation;
+    blocks.push_back(d);
+    bytes += n;
+    if (n) memcpy(d, host.data(), n);
+#else
+    void* d = nullptr;
+    auto  e = cudaMalloc(&d, n ? n : 16);
+    if (e != cudaSuccess) return e;
+    blocks.push_back(d);
+    bytes += n;
+    if (n) {
+      e = cudaMemcpy(d, host.data(), n, cudaMemcpyHostToDevice);
+      if (e != cudaSuccess) return e;
+    }
+#endif
+    *out = (const T*)d;
+    return cudaSuccess;
+  }
+  void release() {
+#if defined(VPT_HOST_POOL)
+    for (auto b : blocks) free(b);
+#else
+    for (auto b : blocks) cudaFree(b);
+#endif
+    blocks.clear();
+    bytes = 0;
+  }
+};
+
+inline f4 pack(f3 v, float w) { return {v.x, v.y, v.z, w}; }
+inline f4 pack(f3 v, int w) { return {v.x, v.y, v.z, i2f(w)}; }
+inline frame3 to_frame(const float* f) {
+  return {{f[0], f[1], f[2]}, {f[3], f[4], f[5]}, {f[6], f[7], f[8]}, {f[9], f[10], f[11]}};
+}
+
+// depth of the deepest leaf (root = 1); -1 on malformed child links
+inline int bvh_depth(const vpt_bvh_desc& b) {
+  if (b.num_nodes <= 0) return 0;
+  std::vector<std::pair<int, int>> stack = {{0, 1}};
+  int                              deepest = 0;
+  size_t                           visited = 0;
+  while (!stack.empty()) {
+    auto [id, depth] = stack.back();
+    stack.pop_back();
+    if (id < 0 || id >= b.num_nodes || ++visited > (size_t)b.num_nodes) return -1;
+    deepest = depth > deepest ? depth : deepest;
+    auto& n = b.nodes[id];
+    if (n.internal) {
+      stack.push_back({n.start, depth + 1});
+      stack.push_back({n.start + 1, depth + 1});
+    }
+  }
+  return deepest;
+}
+
+struct flat_scene {
+  DScene      d{};
+  device_pool pool;
+  int         stack_depth = 1;  // traversal stack entries a thread can need
+  int         num_cameras = 0;
+  std::vector<float> camera_aspect;
+};
+
+// Returns VPT_OK or a negative status and fills `error`.
+inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string& error) {
+  auto fail = [&](int code, const std::string& msg) {
+    error = msg;
+    return code;
+  };
+  if (in.num_cameras < 0 || in.num_instances < 0 || in.num_shapes < 0 || in.num_materials < 0 ||
+      in.num_textures < 0 || in.num_environments < 0 || in.num_volumes < 0 ||
+      in.num_vol_instances < 0 || in.num_sdfs < 0 || in.num_lights < 0)
+    return fail(VPT_ERR_INVALID, "negative element count in scene description");
+  if (in.num_shapes > 0 && !in.shape_bvhs)
+    return fail(VPT_ERR_INVALID, "shape_bvhs is null");
+
+  std::vector<f4>  nodes, prims, inst_trav, inst_frame, vcol, materials, cameras, environments;
+  std::vector<f4>  vol_instances, volumes, sdfs, texf;
+  std::vector<int> scene_prims;
+  std::vector<i4>  shapes, elems, textures, lights;
+  std::vector<float>         vpos, vnrm, vtex, cdf, voxels, srgb_lut(256);
+  std::vector<unsigned char> texb;
+
+  auto push_node = [&](const vpt_bvh_node& n, int start) {
+    nodes.push_back({n.bbox_min[0], n.bbox_min[1], n.bbox_min[2], n.bbox_max[0]});
+    int meta = ((int)n.num & 0xffff) | (((int)n.axis & 0xff) << 16) | ((n.internal ? 1 : 0) << 24);
+    nodes.push_back({n.bbox_max[1], n.bbox_max[2], i2f(start), i2f(meta)});
+  };
+
+  // ---- shapes: vertex pools, element indices, leaf-ordered primitive records ----
+  std::vector<int> shape_root(in.num_shapes, -1), shape_kind(in.num_shapes, kind_empty);
+  int              max_shape_depth = 0;
+  for (int s = 0; s < in.num_shapes; s++) {
+    auto& sh = in.shapes[s];
+    if (sh.num_points > 0 || sh.num_lines > 0)
+      return fail(VPT_ERR_UNSUPPORTED,
+          "shape " + std::to_string(s) + " has point/line primitives (unsupported on the GPU path)");
+    // same precedence as the reference: triangles, then quads
+    int kind  = sh.num_triangles > 0 ? kind_triangles : (sh.num_quads > 0 ? kind_quads : kind_empty);
+    int nelem = kind == kind_triangles ? sh.num_triangles : (kind == kind_quads ? sh.num_quads : 0);
+    shape_kind[s] = kind;
+    int pos_off = (int)(vpos.size() / 3);
+    vpos.insert(vpos.end(), sh.positions, sh.positions + 3 * (size_t)sh.num_positions);
+    int nrm_off = -1, tex_off = -1, col_off = -1;
+    if (sh.num_normals > 0) {
+      nrm_off = (int)(vnrm.size() / 3);
+      vnrm.insert(vnrm.end(), sh.normals, sh.normals + 3 * (size_t)sh.num_normals);
+    }
+    if (sh.num_texcoords > 0) {
+      tex_off = (int)(vtex.size() / 2);
+      vtex.insert(vtex.end(), sh.texcoords, sh.texcoords + 2 * (size_t)sh.num_texcoords);
+    }
+    if (sh.num_colors > 0) {
+      col_off = (int)vcol.size();
+      for (int i = 0; i < sh.num_colors; i++)
+        vcol.push_back({sh.colors[4 * i], sh.colors[4 * i + 1], sh.colors[4 * i + 2],
+            sh.colors[4 * i + 3]});
+    }
+    int elem_off = (int)elems.size();
+    for (int e = 0; e < nelem; e++) {
+      i4 q = kind == kind_triangles
+                 ? i4{sh.triangles[3 * e], sh.triangles[3 * e + 1], sh.triangles[3 * e + 2], -1}
+                 : i4{sh.quads[4 * e], sh.quads[4 * e + 1], sh.quads[4 * e + 2], sh.quads[4 * e + 3]};
+      int nv = kind == kind_triangles ? 3 : 4;
+      int v[4] = {q.x, q.y, q.z, q.w};
+      for (int k = 0; k < nv; k++)
+        if (v[k] < 0 || v[k] >= sh.num_positions)
+          return fail(VPT_ERR_INVALID, "vertex index out of range in shape " + std::to_string(s));
+      elems.push_back(q);
+    }
+    shapes.push_back({kind, pos_off, nrm_off, tex_off});
+    shapes.push_back({col_off, elem_off, 0, 0});
+
+    if (kind == kind_empty) continue;
+    auto& bvh = in.shape_bvhs[s];
+    if (bvh.num_nodes <= 0 || bvh.num_primitives != nelem)
+      return fail(VPT_ERR_INVALID, "shape bvh " + std::to_string(s) + " does not match its shape");
+    int depth = bvh_depth(bvh);
+    if (depth < 0) return fail(VPT_ERR_INVALID, "malformed shape bvh " + std::to_string(s));
+    max_shape_depth = depth > max_shape_depth ? depth : max_shape_depth;
+    int stride    = kind == kind_triangles ? 3 : 4;
+    int node_base = (int)(nodes.size() / 2);
+    int prim_base = (int)prims.size();
+    shape_root[s] = node_base;
+    for (int k = 0; k < bvh.num_primitives; k++) {
+      int e = bvh.primitives[k];
+      if (e < 0 || e >= nelem)
+        return fail(VPT_ERR_INVALID, "bvh primitive out of range in shape " + std::to_string(s));
+      auto q   = elems[elem_off + e];
+      int  v[4] = {q.x, q.y, q.z, q.w};
+      for (int c = 0; c < stride; c++) {
+        auto p = sh.positions + 3 * (size_t)v[c];
+        prims.push_back({p[0], p[1], p[2], i2f(e)});
+      }
+    }
+    for (int n = 0; n < bvh.num_nodes; n++) {
+      auto& node = bvh.nodes[n];
+      if (node.internal) {
+        push_node(node, node_base + node.start);
+      } else {
+        if (node.start < 0 || node.start + node.num > bvh.num_primitives)
+          return fail(VPT_ERR_INVALID, "bvh leaf out of range in shape " + std::to_string(s));
+        push_node(node, prim_base + node.start * stride);
+      }
+    }
+  }
+
+  // ---- instances + scene bvh ----------------------------------------------------
+  for (int i = 0; i < in.num_instances; i++) {
+    auto& inst = in.instances[i];
+    if (inst.shape < 0 || inst.shape >= in.num_shapes || inst.material < 0 ||
+        inst.material >= in.num_materials)
+      return fail(VPT_ERR_INVALID, "instance " + std::to_string(i) + " references a missing shape/material");
+    auto frame = to_frame(inst.frame);
+    auto inv   = inverse_frame(frame, true);  // yocto_bvh.cpp:854-855
+    inst_trav.push_back(pack(inv.x, shape_root[inst.shape]));
+    inst_trav.push_back(pack(inv.y, shape_kind[inst.shape]));
+    inst_trav.push_back(pack(inv.z, inst.shape));
+    inst_trav.push_back(pack(inv.o, inst.material));
+    inst_frame.push_back(pack(frame.x, inst.shape));
+    inst_frame.push_back(pack(frame.y, inst.material));
+    inst_frame.push_back(pack(frame.z, 0));
+    inst_frame.push_back(pack(frame.o, 0));
+  }
+  int scene_root = -1, scene_depth = 0;
+  if (in.num_instances > 0) {
+    auto& bvh = in.scene_bvh;
+    if (bvh.num_nodes <= 0 || bvh.num_primitives != in.num_instances)
+      return fail(VPT_ERR_INVALID, "scene bvh does not match the instance list");
+    scene_depth = bvh_depth(bvh);
+    if (scene_depth < 0) return fail(VPT_ERR_INVALID, "malformed scene bvh");
+    scene_root = (int)(nodes.size() / 2);
+    for (int k = 0; k < bvh.num_primitives; k++) {
+      if (bvh.primitives[k] < 0 || bvh.primitives[k] >= in.num_instances)
+        return fail(VPT_ERR_INVALID, "scene bvh primitive out of range");
+      scene_prims.push_back(bvh.primitives[k]);
+    }
+    for (int n = 0; n < bvh.num_nodes; n++) {
+      auto& node = bvh.nodes[n];
+      push_node(node, node.internal ? scene_root + node.start : node.start);
+    }
+  }
+  // DFS with the near child in a register keeps at most one entry per level
+  out.stack_depth = max_shape_depth + scene_depth + 2;
+  if (out.stack_depth > vpt_stack_depth)
+    return fail(VPT_ERR_UNSUPPORTED, "bvh deeper than the device traversal stack (" +
+                                         std::to_string(out.stack_depth) + " > " +
+                                         std::to_string(vpt_stack_depth) + ")");
+
+  // ---- materials, textures ---------------------------------------------------------
+  for (int m = 0; m < in.num_materials; m++) {
+    auto& mt = in.materials[m];
+    materials.push_back({i2f(mt.type), mt.emission[0], mt.emission[1], mt.emission[2]});
+    materials.push_back({mt.color[0], mt.color[1], mt.color[2], mt.roughness});
+    materials.push_back({mt.metallic, mt.ior, mt.scattering[0], mt.scattering[1]});
+    materials.push_back({mt.scattering[2], mt.scanisotropy, mt.trdepth, mt.opacity});
+    materials.push_back({i2f(mt.emission_tex), i2f(mt.color_tex), i2f(mt.roughness_tex),
+        i2f(mt.scattering_tex)});
+    materials.push_back({i2f(mt.normal_tex), 0, 0, 0});
+  }
+  for (int t = 0; t < in.num_textures; t++) {
+    auto&  tx = in.textures[t];
+    size_t n  = (size_t)tx.width * tx.height;
+    if (tx.pixelsf) {
+      textures.push_back({tx.width, tx.height, (tx.linear ? 1 : 0) | 2, (int)texf.size()});
+      for (size_t i = 0; i < n; i++)
+        texf.push_back({tx.pixelsf[4 * i], tx.pixelsf[4 * i + 1], tx.pixelsf[4 * i + 2],
+            tx.pixelsf[4 * i + 3]});
+    } else if (tx.pixelsb) {
+      textures.push_back({tx.width, tx.height, (tx.linear ? 1 : 0), (int)(texb.size() / 4)});
+      texb.insert(texb.end(), tx.pixelsb, tx.pixelsb + 4 * n);
+    } else {
+      textures.push_back({0, 0, 0, 0});
+    }
+  }
+  // srgb_to_rgb(byte / 255.0f) with the host libm (yocto_color.h:212-226)
+  for (int b = 0; b < 256; b++) {
+    float srgb  = b / 255.0f;
+    srgb_lut[b] = ((double)srgb <= 0.04045) ? srgb / 12.92f
+                                            : powf((srgb + 0.055f) / (1.0f + 0.055f), 2.4f);
+  }
+
+  // ---- cameras, environments, lights -----------------------------------------------
+  for (int c = 0; c < in.num_cameras; c++) {
+    auto& cm    = in.cameras[c];
+    auto  frame = to_frame(cm.frame);
+    cameras.push_back(pack(frame.x, cm.orthographic ? 1 : 0));
+    cameras.push_back(pack(frame.y, cm.lens));
+    cameras.push_back(pack(frame.z, cm.film));
+    cameras.push_back(pack(frame.o, cm.aspect));
+    cameras.push_back({cm.focus, cm.aperture, 0, 0});
+    out.camera_aspect.push_back(cm.aspect);
+  }
+  out.num_cameras = in.num_cameras;
+  for (int e = 0; e < in.num_environments; e++) {
+    auto& ev    = in.environments[e];
+    auto  frame = to_frame(ev.frame);
+    auto  inv   = inverse_frame(frame, false);  // inverse(environment.frame): rigid
+    if (ev.emission_tex >= in.num_textures)
+      return fail(VPT_ERR_INVALID, "environment texture out of range");
+    environments.push_back(pack(frame.x, 0)), environments.push_back(pack(frame.y, 0));
+    environments.push_back(pack(frame.z, 0)), environments.push_back(pack(frame.o, 0));
+    environments.push_back(pack(inv.x, 0)), environments.push_back(pack(inv.y, 0));
+    environments.push_back(pack(inv.z, 0)), environments.push_back(pack(inv.o, 0));
+    environments.push_back({ev.emission[0], ev.emission[1], ev.emission[2], i2f(ev.emission_tex)});
+  }
+  for (int l = 0; l < in.num_lights; l++) {
+    auto& lt = in.lights[l];
+    if (lt.instance >= in.num_instances || lt.environment >= in.num_environments ||
+        lt.sdf >= in.num_sdfs)
+      return fail(VPT_ERR_INVALID, "light " + std::to_string(l) + " references a missing object");
+    lights.push_back({lt.instance, lt.environment, lt.sdf, (int)cdf.size()});
+    lights.push_back({lt.num_elements, 0, 0, 0});
+    if (lt.num_elements > 0) cdf.insert(cdf.end(), lt.elements_cdf, lt.elements_cdf + lt.num_elements);
+  }
+
+  // ---- sdf grids and functions -------------------------------------------------------
+  for (int v = 0; v < in.num_volumes; v++) {
+    auto&  vol = in.volumes[v];
+    size_t n   = (size_t)vol.whd[0] * vol.whd[1] * vol.whd[2];
+    volumes.push_back({i2f(vol.whd[0]), i2f(vol.whd[1]), i2f(vol.whd[2]), vol.res});
+    volumes.push_back({i2f((int)voxels.size()), 0, 0, 0});
+    voxels.insert(voxels.end(), vol.voxels, vol.voxels + n);
+  }
+  for (int v = 0; v < in.num_vol_instances; v++) {
+    auto& vi = in.vol_instances[v];
+    if (vi.volume < 0 || vi.volume >= in.num_volumes || vi.material < 0 ||
+        vi.material >= in.num_materials)
+      return fail(VPT_ERR_INVALID, "sdf grid instance references a missing volume/material");
+    auto frame = to_frame(vi.frame);
+    vol_instances.push_back(pack(frame.x, vi.scalef));
+    vol_instances.push_back(pack(frame.y, vi.volume));
+    vol_instances.push_back(pack(frame.z, vi.material));
+    vol_instances.push_back(pack(frame.o, 0));
+  }
+  for (int s = 0; s < in.num_sdfs; s++) {
+    auto& sd = in.sdfs[s];
+    if (sd.type < 0 || sd.type > VPT_SDF_TORUS || sd.material < 0 || sd.material >= in.num_materials)
+      return fail(VPT_ERR_INVALID, "sdf " + std::to_string(s) + " has a bad type/material");
+    auto frame = to_frame(sd.frame);
+    auto inv   = inverse_frame(frame, false);  // yocto_pathtrace.cpp:330
+    sdfs.push_back(pack(frame.x, sd.type)), sdfs.push_back(pack(frame.y, sd.material));
+    sdfs.push_back(pack(frame.z, 0)), sdfs.push_back(pack(frame.o, 0));
+    sdfs.push_back(pack(inv.x, 0)), sdfs.push_back(pack(inv.y, 0));
+    sdfs.push_back(pack(inv.z, 0)), sdfs.push_back(pack(inv.o, 0));
+    sdfs.push_back({sd.params[0], sd.params[1], sd.params[2], sd.params[3]});
+    sdfs.push_back({sd.whd[0], sd.whd[1], sd.whd[2], 0});
+  }
+
+  // ---- to the device -----------------------------------------------------------------
+  auto& d = out.d;
+  auto& p = out.pool;
+  cudaError_t e = cudaSuccess;
+#define VPT_UP(vec, field) \
+  if (e == cudaSuccess) e = p.upload(vec, &d.field)
+  VPT_UP(nodes, nodes);
+  VPT_UP(prims, prims);
+  VPT_UP(scene_prims, scene_prims);
+  VPT_UP(inst_trav, inst_trav);
+  VPT_UP(inst_frame, inst_frame);
+  VPT_UP(shapes, shapes);
+  VPT_UP(vpos, vpos);
+  VPT_UP(vnrm, vnrm);
+  VPT_UP(vtex, vtex);
+  VPT_UP(vcol, vcol);
+  VPT_UP(elems, elems);
+  VPT_UP(materials, materials);
+  VPT_UP(textures, textures);
+  VPT_UP(texb, texb);
+  VPT_UP(texf, texf);
+  VPT_UP(srgb_lut, srgb_lut);
+  VPT_UP(cameras, cameras);
+  VPT_UP(environments, environments);
+  VPT_UP(lights, lights);
+  VPT_UP(cdf, cdf);
+  VPT_UP(vol_instances, vol_instances);
+  VPT_UP(volumes, volumes);
+  VPT_UP(voxels, voxels);
+  VPT_UP(sdfs, sdfs);
+#undef VPT_UP
+  if (e != cudaSuccess) {
+    p.release();
+    return fail(e == cudaErrorMemoryAllocation ? VPT_ERR_OUT_OF_MEMORY : VPT_ERR_CUDA,
+        std::string("scene upload failed: ") + cudaGetErrorString(e));
+  }
+  d.scene_root        = scene_root;
+  d.num_instances     = in.num_instances;
+  d.num_environments  = in.num_environments;
+  d.num_lights        = in.num_lights;
+  d.num_vol_instances = in.num_vol_instances;
+  d.num_sdfs          = in.num_sdfs;
+  return VPT_OK;
+}
+
+}  // namespace vpt

@@ -1,0 +1,446 @@
+// vpt_cuda.cu — kernels and the extern "C" layer of include/vpt_cuda.h.
+//
+// Built for sm_100a only, with -fmad=false so that the traversal and the
+// deterministic shaders reproduce the reference's IEEE arithmetic bit for bit.
+// There is no CPU fallback in this library: every compute entry point needs a
+// CUDA device and fails with VPT_ERR_NO_DEVICE otherwise.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <new>
+#include <string>
+
+#include "../../include/vpt_cuda.h"
+#include "shaders.cuh"
+#include "tiling.cuh"
+#include "upload.cuh"
+#include "wavefront.cuh"
+
+using namespace vpt;
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+static int set_error(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+static int cuda_fail(cudaError_t e, const char* what) {
+  return set_error(e == cudaErrorMemoryAllocation ? VPT_ERR_OUT_OF_MEMORY : VPT_ERR_CUDA,
+      std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define VPT_CUDA_TRY(call)                               \
+  do {                                                   \
+    cudaError_t e_ = (call);                             \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #call);  \
+  } while (0)
+
+static int require_device() {
+  int  n = 0;
+  auto e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return set_error(VPT_ERR_NO_DEVICE,
+        "no CUDA device available: the B200 path has no CPU fallback");
+  }
+  return VPT_OK;
+}
+
+// ---------------------------------------------------------------------------
+// opaque handles
+// ---------------------------------------------------------------------------
+struct vpt_scene {
+  flat_scene flat;
+  int        device = 0;
+};
+
+struct vpt_state {
+  int             width = 0, height = 0, samples = 0;
+  int             device = 0;
+  f4*             image  = nullptr;
+  rng_t*          rngs   = nullptr;
+  wavefront_buffers wf;
+  cudaEvent_t     ev0 = nullptr, ev1 = nullptr;
+  vpt_trace_stats stats{};
+};
+
+// ---------------------------------------------------------------------------
+// megakernel: one thread owns one pixel and runs whole paths for `nsamples`
+// samples; the pixel's generator never leaves registers.
+// ---------------------------------------------------------------------------
+constexpr int mega_block = 128;
+
+template <int S>
+__global__ void __launch_bounds__(mega_block)
+    k_render_mega(const DScene sc, const DParams prm, f4* __restrict__ image,
+        rng_t* __restrict__ rngs, int npixels, int nsamples) {
+  extern __shared__ int stack_mem[];
+  // 8x4 pixel tiles per warp keep neighbouring lanes on neighbouring rays
+  int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  int idx = tile_pixel_index(tid, prm.width, prm.height);
+  if (idx < 0) return;
+  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  auto    rng = rngs[idx];
+  auto    acc = image[idx];
+  for (int s = 0; s < nsamples; s++) {
+    auto ray = sample_camera(sc, prm, idx, rng);
+    auto rad = guard_radiance(shade_path<S>(sc, prm, ray, rng, st));
+    acc      = acc + rad;
+  }
+  image[idx] = acc;
+  rngs[idx]  = rng;
+}
+
+// first-hit queries for ray batches (parity gate for the traversal)
+__global__ void __launch_bounds__(mega_block)
+    k_intersect(const DScene sc, const float* __restrict__ rays, int n, int instance,
+        int* __restrict__ ids, float* __restrict__ uvd) {
+  extern __shared__ int stack_mem[];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  auto    r   = rays + 8 * (size_t)i;
+  auto    ray = ray3{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}, r[6], r[7]};
+  auto    h   = instance >= 0 ? intersect_instance(sc, instance, ray, st)
+                              : intersect_scene(sc, ray, st);
+  ids[3 * i + 0] = h.hit ? 1 : 0;
+  ids[3 * i + 1] = h.hit ? h.instance : -1;
+  ids[3 * i + 2] = h.hit ? h.element : -1;
+  uvd[3 * i + 0] = h.hit ? h.uv.x : 0;
+  uvd[3 * i + 1] = h.hit ? h.uv.y : 0;
+  uvd[3 * i + 2] = h.hit ? h.distance : 0;
+}
+
+__global__ void __launch_bounds__(mega_block)
+    k_spheretrace(const DScene sc, const float* __restrict__ rays, int n, int maxiter,
+        int* __restrict__ ids, float* __restrict__ dn) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  auto r   = rays + 8 * (size_t)i;
+  auto ray = ray3{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}, r[6], r[7]};
+  auto st  = spheretrace(sc, ray, maxiter);
+  auto nrm = f3{0, 0, 0};
+  if (st.hit) {
+    auto pos = ray_point(ray, st.dist);
+    nrm      = st.instance != invalidid
+                   ? eval_sdf_normal_grid(sc, ld_vol_instance(sc, st.instance), pos, st.dist)
+                   : eval_sdf_normal_fn(ld_sdf(sc, st.sdf), pos, st.dist);
+  }
+  ids[3 * i + 0] = st.hit ? 1 : 0;
+  ids[3 * i + 1] = st.hit ? st.instance : -1;
+  ids[3 * i + 2] = st.hit ? st.sdf : -1;
+  dn[4 * i + 0]  = st.hit ? st.dist : 0;
+  dn[4 * i + 1] = nrm.x, dn[4 * i + 2] = nrm.y, dn[4 * i + 3] = nrm.z;
+}
+
+__global__ void k_advance_rngs(rng_t* rngs, int n, unsigned long long delta) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  auto r = rngs[i];
+  rng_advance(r, delta);
+  rngs[i] = r;
+}
+
+// dst[i] += sum over peers of peers[k][i]; peers are P2P-mapped device pointers
+struct peer_list {
+  const float* p[16];
+};
+__global__ void k_reduce_images(float* __restrict__ dst, peer_list peers, int npeers, size_t n4) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  auto acc = reinterpret_cast<float4*>(dst)[i];
+  for (int k = 0; k < npeers; k++) {
+    auto v = reinterpret_cast<const float4*>(peers.p[k])[i];
+    acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+  }
+  reinterpret_cast<float4*>(dst)[i] = acc;
+}
+
+// ---------------------------------------------------------------------------
+// launch helpers
+// ---------------------------------------------------------------------------
+template <int S>
+static cudaError_t launch_mega(const vpt_scene* scene, vpt_state* state, const DParams& prm,
+    int nsamples) {
+  int    npix   = state->width * state->height;
+  int    slots  = tile_slot_count(state->width, state->height);
+  int    blocks = (slots + mega_block - 1) / mega_block;
+  size_t smem   = (size_t)scene->flat.stack_depth * mega_block * sizeof(int);
+  auto   kernel = k_render_mega<S>;
+  if (smem > 48 * 1024) {
+    auto e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  kernel<<<blocks, mega_block, smem>>>(scene->flat.d, prm, state->image, state->rngs, npix,
+      nsamples);
+  return cudaGetLastError();
+}
+
+static cudaError_t dispatch_mega(const vpt_scene* scene, vpt_state* state, const DParams& prm,
+    int nsamples) {
+  switch (prm.shader) {
+    case shader_volpathtrace: return launch_mega<shader_volpathtrace>(scene, state, prm, nsamples);
+    case shader_pathtrace: return launch_mega<shader_pathtrace>(scene, state, prm, nsamples);
+    case shader_naive: return launch_mega<shader_naive>(scene, state, prm, nsamples);
+    case shader_eyelight: return launch_mega<shader_eyelight>(scene, state, prm, nsamples);
+    case shader_normal: return launch_mega<shader_normal>(scene, state, prm, nsamples);
+    case shader_texcoord: return launch_mega<shader_texcoord>(scene, state, prm, nsamples);
+    case shader_color: return launch_mega<shader_color>(scene, state, prm, nsamples);
+    case shader_implicit: return launch_mega<shader_implicit>(scene, state, prm, nsamples);
+    default: return launch_mega<shader_implicit_normal>(scene, state, prm, nsamples);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+extern "C" {
+
+int vpt_cuda_device_count(void) {
+  int  n = 0;
+  auto e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int vpt_cuda_set_device(int device) {
+  if (auto r = require_device()) return r;
+  VPT_CUDA_TRY(cudaSetDevice(device));
+  return VPT_OK;
+}
+
+const char* vpt_cuda_last_error(void) { return g_last_error.c_str(); }
+
+int vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out) {
+  if (!desc || !out) return set_error(VPT_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (auto r = require_device()) return r;
+  auto scene = new (std::nothrow) vpt_scene();
+  if (!scene) return set_error(VPT_ERR_OUT_OF_MEMORY, "host allocation failed");
+  cudaGetDevice(&scene->device);
+  std::string error;
+  auto        r = flatten_scene(*desc, scene->flat, error);
+  if (r != VPT_OK) {
+    delete scene;
+    return set_error(r, error);
+  }
+  *out = scene;
+  return VPT_OK;
+}
+
+void vpt_cuda_free_scene(vpt_scene* scene) {
+  if (!scene) return;
+  scene->flat.pool.release();
+  delete scene;
+}
+
+size_t vpt_cuda_scene_bytes(const vpt_scene* scene) { return scene ? scene->flat.pool.bytes : 0; }
+
+int vpt_cuda_create_state(int width, int height, const uint64_t* rngs, vpt_state** out) {
+  if (!out || width <= 0 || height <= 0) return set_error(VPT_ERR_INVALID, "bad state size");
+  *out = nullptr;
+  if (auto r = require_device()) return r;
+  auto state = new (std::nothrow) vpt_state();
+  if (!state) return set_error(VPT_ERR_OUT_OF_MEMORY, "host allocation failed");
+  state->width = width, state->height = height;
+  cudaGetDevice(&state->device);
+  size_t n = (size_t)width * height;
+  auto   e = cudaMalloc(&state->image, n * sizeof(f4));
+  if (e == cudaSuccess) e = cudaMalloc(&state->rngs, n * sizeof(rng_t));
+  if (e == cudaSuccess) e = cudaEventCreate(&state->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&state->ev1);
+  if (e != cudaSuccess) {
+    vpt_cuda_free_state(state);
+    return cuda_fail(e, "state allocation");
+  }
+  auto r = vpt_cuda_reset_state(state, rngs);
+  if (r != VPT_OK) {
+    vpt_cuda_free_state(state);
+    return r;
+  }
+  *out = state;
+  return VPT_OK;
+}
+
+int vpt_cuda_reset_state(vpt_state* state, const uint64_t* rngs) {
+  if (!state) return set_error(VPT_ERR_INVALID, "null state");
+  size_t n = (size_t)state->width * state->height;
+  VPT_CUDA_TRY(cudaMemsetAsync(state->image, 0, n * sizeof(f4)));
+  if (rngs) {
+    VPT_CUDA_TRY(cudaMemcpyAsync(state->rngs, rngs, n * sizeof(rng_t), cudaMemcpyHostToDevice));
+  } else {
+    VPT_CUDA_TRY(cudaMemsetAsync(state->rngs, 0, n * sizeof(rng_t)));
+  }
+  state->samples = 0;
+  state->wf.live = false;
+  return VPT_OK;
+}
+
+int vpt_cuda_advance_rngs(vpt_state* state, uint64_t delta) {
+  if (!state) return set_error(VPT_ERR_INVALID, "null state");
+  int n = state->width * state->height;
+  k_advance_rngs<<<(n + 255) / 256, 256>>>(state->rngs, n, delta);
+  VPT_CUDA_TRY(cudaGetLastError());
+  return VPT_OK;
+}
+
+void vpt_cuda_free_state(vpt_state* state) {
+  if (!state) return;
+  cudaFree(state->image);
+  cudaFree(state->rngs);
+  state->wf.release();
+  if (state->ev0) cudaEventDestroy(state->ev0);
+  if (state->ev1) cudaEventDestroy(state->ev1);
+  delete state;
+}
+
+int vpt_cuda_state_samples(const vpt_state* state) { return state ? state->samples : 0; }
+
+int vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params* params,
+    int nsamples) {
+  if (!scene || !state || !params) return set_error(VPT_ERR_INVALID, "null argument");
+  if (params->shader < 0 || params->shader >= VPT_SHADER_COUNT)
+    return set_error(VPT_ERR_INVALID, "sampler unknown");  // get_shader, yocto_pathtrace.cpp:948
+  if (params->camera < 0 || params->camera >= scene->flat.num_cameras)
+    return set_error(VPT_ERR_INVALID, "camera index out of range");
+  state->stats = vpt_trace_stats{};
+  int todo = std::min(nsamples, params->samples - state->samples);
+  if (todo <= 0) return VPT_OK;  // yocto_pathtrace.cpp:1055
+
+  DParams prm{};
+  prm.camera              = params->camera;
+  prm.shader              = params->shader;
+  prm.samples             = params->samples;
+  prm.bounces             = params->bounces;
+  prm.noimplicit_mis      = params->noimplicit_mis;
+  prm.spheretrace_maxiter = params->spheretrace_maxiter;
+  prm.width = state->width, prm.height = state->height;
+
+  bool path_shader = prm.shader == shader_volpathtrace || prm.shader == shader_pathtrace ||
+                     prm.shader == shader_naive || prm.shader == shader_implicit;
+  bool wavefront = params->pipeline == VPT_PIPELINE_WAVEFRONT ||
+                   (params->pipeline == VPT_PIPELINE_AUTO && path_shader && false);
+
+  VPT_CUDA_TRY(cudaEventRecord(state->ev0));
+  int launches = 0;
+  if (wavefront && path_shader) {
+    auto e = run_wavefront(scene->flat, state->wf, prm, state->image, state->rngs, todo,
+        &launches, &state->stats);
+    if (e != cudaSuccess) return cuda_fail(e, "wavefront pipeline");
+  } else {
+    auto e = dispatch_mega(scene, state, prm, todo);
+    if (e != cudaSuccess) return cuda_fail(e, "megakernel launch");
+    launches = 1;
+  }
+  VPT_CUDA_TRY(cudaEventRecord(state->ev1));
+  VPT_CUDA_TRY(cudaEventSynchronize(state->ev1));
+  VPT_CUDA_TRY(cudaGetLastError());
+  float ms = 0;
+  VPT_CUDA_TRY(cudaEventElapsedTime(&ms, state->ev0, state->ev1));
+  state->samples += todo;
+  state->stats.device_ms       = ms;
+  if (state->stats.top_kernel_ms == 0) state->stats.top_kernel_ms = ms;
+  state->stats.kernel_launches = launches;
+  state->stats.paths           = (uint64_t)todo * state->width * state->height;
+  return VPT_OK;
+}
+
+int vpt_cuda_get_trace_stats(const vpt_state* state, vpt_trace_stats* stats) {
+  if (!state || !stats) return set_error(VPT_ERR_INVALID, "null argument");
+  *stats = state->stats;
+  return VPT_OK;
+}
+
+int vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n) {
+  if (!state || !rgba) return set_error(VPT_ERR_INVALID, "null argument");
+  size_t want = (size_t)state->width * state->height * 4;
+  if (n != want) return set_error(VPT_ERR_INVALID, "image should have the same size");
+  VPT_CUDA_TRY(cudaMemcpy(rgba, state->image, want * sizeof(float), cudaMemcpyDeviceToHost));
+  return VPT_OK;
+}
+
+int vpt_cuda_download_rngs(vpt_state* state, uint64_t* rngs, size_t n) {
+  if (!state || !rngs) return set_error(VPT_ERR_INVALID, "null argument");
+  size_t want = (size_t)state->width * state->height * 2;
+  if (n != want) return set_error(VPT_ERR_INVALID, "rng buffer should have the same size");
+  VPT_CUDA_TRY(cudaMemcpy(rngs, state->rngs, want * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  return VPT_OK;
+}
+
+void* vpt_cuda_image_device_ptr(vpt_state* state) { return state ? state->image : nullptr; }
+
+int vpt_cuda_intersect(vpt_scene* scene, const float* rays, int n, int instance, int32_t* ids,
+    float* uvd) {
+  if (!scene || !rays || !ids || !uvd || n < 0) return set_error(VPT_ERR_INVALID, "bad argument");
+  if (instance >= scene->flat.d.num_instances)
+    return set_error(VPT_ERR_INVALID, "instance out of range");
+  if (n == 0) return VPT_OK;
+  float* d_rays = nullptr;
+  int*   d_ids  = nullptr;
+  float* d_uvd  = nullptr;
+  auto   e      = cudaMalloc(&d_rays, (size_t)n * 8 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&d_ids, (size_t)n * 3 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(&d_uvd, (size_t)n * 3 * sizeof(float));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(d_rays, rays, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    size_t smem = (size_t)scene->flat.stack_depth * mega_block * sizeof(int);
+    if (smem > 48 * 1024)
+      e = cudaFuncSetAttribute(k_intersect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) {
+      k_intersect<<<(n + mega_block - 1) / mega_block, mega_block, smem>>>(scene->flat.d, d_rays,
+          n, instance, d_ids, d_uvd);
+      e = cudaGetLastError();
+    }
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(ids, d_ids, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(uvd, d_uvd, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d_rays), cudaFree(d_ids), cudaFree(d_uvd);
+  if (e != cudaSuccess) return cuda_fail(e, "vpt_cuda_intersect");
+  return VPT_OK;
+}
+
+int vpt_cuda_spheretrace(vpt_scene* scene, const float* rays, int n, int maxiter, int32_t* ids,
+    float* dn) {
+  if (!scene || !rays || !ids || !dn || n < 0) return set_error(VPT_ERR_INVALID, "bad argument");
+  if (n == 0) return VPT_OK;
+  float* d_rays = nullptr;
+  int*   d_ids  = nullptr;
+  float* d_dn   = nullptr;
+  auto   e      = cudaMalloc(&d_rays, (size_t)n * 8 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&d_ids, (size_t)n * 3 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(&d_dn, (size_t)n * 4 * sizeof(float));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(d_rays, rays, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    k_spheretrace<<<(n + mega_block - 1) / mega_block, mega_block>>>(scene->flat.d, d_rays, n,
+        maxiter, d_ids, d_dn);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(ids, d_ids, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(dn, d_dn, (size_t)n * 4 * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d_rays), cudaFree(d_ids), cudaFree(d_dn);
+  if (e != cudaSuccess) return cuda_fail(e, "vpt_cuda_spheretrace");
+  return VPT_OK;
+}
+
+int vpt_cuda_reduce_images(float* dst, const float* const* peers, int npeers, size_t count) {
+  if (!dst || (npeers > 0 && !peers) || npeers < 0 || npeers > 16 || (count & 3))
+    return set_error(VPT_ERR_INVALID, "bad argument");
+  if (npeers == 0 || count == 0) return VPT_OK;
+  peer_list pl{};
+  for (int k = 0; k < npeers; k++) pl.p[k] = peers[k];
+  size_t n4 = count / 4;
+  k_reduce_images<<<(unsigned)((n4 + 255) / 256), 256>>>(dst, pl, npeers, n4);
+  VPT_CUDA_TRY(cudaGetLastError());
+  VPT_CUDA_TRY(cudaDeviceSynchronize());
+  return VPT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,263 @@
+// vpt_host_c.cpp — extern "C" wrappers of the C++ facade (include/vpt_host.h),
+// used by the Python tests / bench through ctypes. Exceptions never cross the
+// C boundary: they become a negative status + vpth_last_error().
+#include <cstring>
+
+#include "../../include/vpt_host.h"
+#include "vpt_pathtrace.h"
+
+using namespace vpt;
+
+struct vpth_scene {
+  scene_data                    scene;
+  bvh_scene                     bvh;
+  pathtrace_lights              lights;
+  std::shared_ptr<device_scene> device;
+};
+
+struct vpth_render {
+  vpth_scene*            owner = nullptr;
+  pathtrace_params       params;
+  pathtrace_state        state;
+  std::vector<rng_state> initial_rngs;
+};
+
+static thread_local std::string g_error;
+
+template <typename F>
+static int guarded(F&& f) {
+  try {
+    f();
+    return VPT_OK;
+  } catch (std::invalid_argument& e) {
+    g_error = e.what();
+    return VPT_ERR_INVALID;
+  } catch (std::exception& e) {
+    g_error = e.what();
+    auto msg = std::string(e.what());
+    if (msg.find("no CUDA device") != std::string::npos) return VPT_ERR_NO_DEVICE;
+    if (msg.find("unsupported") != std::string::npos ||
+        msg.find("not supported") != std::string::npos)
+      return VPT_ERR_UNSUPPORTED;
+    return VPT_ERR_CUDA;
+  }
+}
+
+static vpt_scene* device_scene_of(vpth_scene* s) {
+  if (!s->device) s->device = upload_scene(s->scene, s->bvh, s->lights);
+  return device_handle(s->device);
+}
+
+static pathtrace_params from_c_params(const vpt_params& c) {
+  auto p = pathtrace_params{};
+  p.camera = c.camera, p.resolution = c.resolution, p.shader = (pathtrace_shader_type)c.shader;
+  p.samples = c.samples, p.bounces = c.bounces, p.noparallel = c.noparallel != 0;
+  p.pratio = c.pratio, p.exposure = c.exposure, p.filmic = c.filmic != 0;
+  p.noimplicit_mis = c.noimplicit_mis != 0, p.spheretrace_maxiter = c.spheretrace_maxiter;
+  p.pipeline = (pathtrace_pipeline)c.pipeline;
+  return p;
+}
+
+extern "C" {
+
+const char* vpth_last_error(void) { return g_error.c_str(); }
+
+int vpth_load_scene(const char* path, vpth_scene** out) {
+  if (!path || !out) {
+    g_error = "null argument";
+    return VPT_ERR_INVALID;
+  }
+  *out   = nullptr;
+  auto s = new vpth_scene();
+  auto r = guarded([&] {
+    auto error = std::string{};
+    if (!load_scene(path, s->scene, error)) throw std::invalid_argument(error);
+    auto params = pathtrace_params{};
+    s->bvh      = make_bvh(s->scene, params);
+    s->lights   = make_lights(s->scene, params);
+  });
+  if (r != VPT_OK) {
+    delete s;
+    return r;
+  }
+  *out = s;
+  return VPT_OK;
+}
+
+void vpth_free_scene(vpth_scene* scene) { delete scene; }
+
+int vpth_scene_counts(const vpth_scene* s, int32_t counts[12]) {
+  if (!s || !counts) return VPT_ERR_INVALID;
+  size_t shape_nodes = 0;
+  for (auto& b : s->bvh.shapes) shape_nodes += b.nodes.size();
+  size_t v[12] = {s->scene.cameras.size(), s->scene.instances.size(), s->scene.shapes.size(),
+      s->scene.materials.size(), s->scene.textures.size(), s->scene.environments.size(),
+      s->scene.volumes.size(), s->scene.vol_instances.size(), s->scene.sdfs.size(),
+      s->lights.lights.size(), s->bvh.nodes.size(), shape_nodes};
+  for (int i = 0; i < 12; i++) counts[i] = (int32_t)v[i];
+  return VPT_OK;
+}
+
+static const bvh_data* pick_bvh(const vpth_scene* s, int shape) {
+  if (shape < 0) return &s->bvh;
+  if (shape >= (int)s->bvh.shapes.size()) return nullptr;
+  return &s->bvh.shapes[shape];
+}
+
+int vpth_bvh_size(const vpth_scene* s, int shape, int32_t* num_nodes, int32_t* num_prims) {
+  auto b = s ? pick_bvh(s, shape) : nullptr;
+  if (!b || !num_nodes || !num_prims) return VPT_ERR_INVALID;
+  *num_nodes = (int32_t)b->nodes.size(), *num_prims = (int32_t)b->primitives.size();
+  return VPT_OK;
+}
+
+int vpth_bvh_copy(const vpth_scene* s, int shape, vpt_bvh_node* nodes, int32_t* prims) {
+  auto b = s ? pick_bvh(s, shape) : nullptr;
+  if (!b || !nodes || !prims) return VPT_ERR_INVALID;
+  memcpy(nodes, b->nodes.data(), b->nodes.size() * sizeof(vpt_bvh_node));
+  memcpy(prims, b->primitives.data(), b->primitives.size() * sizeof(int32_t));
+  return VPT_OK;
+}
+
+int vpth_light_info(const vpth_scene* s, int light, int32_t ids[3], int32_t* cdf_size) {
+  if (!s || light < 0 || light >= (int)s->lights.lights.size() || !ids || !cdf_size)
+    return VPT_ERR_INVALID;
+  auto& l = s->lights.lights[light];
+  ids[0] = l.instance, ids[1] = l.environment, ids[2] = l.sdf;
+  *cdf_size = (int32_t)l.elements_cdf.size();
+  return VPT_OK;
+}
+
+int vpth_light_cdf(const vpth_scene* s, int light, float* cdf) {
+  if (!s || light < 0 || light >= (int)s->lights.lights.size() || !cdf) return VPT_ERR_INVALID;
+  auto& l = s->lights.lights[light];
+  memcpy(cdf, l.elements_cdf.data(), l.elements_cdf.size() * sizeof(float));
+  return VPT_OK;
+}
+
+int vpth_render_create(vpth_scene* scene, const vpt_params* params, vpth_render** out) {
+  if (!scene || !params || !out) {
+    g_error = "null argument";
+    return VPT_ERR_INVALID;
+  }
+  *out   = nullptr;
+  auto r = new vpth_render();
+  auto e = guarded([&] {
+    if (params->camera < 0 || params->camera >= (int)scene->scene.cameras.size())
+      throw std::invalid_argument("camera index out of range");
+    r->owner        = scene;
+    r->params       = from_c_params(*params);
+    r->state        = make_state(scene->scene, r->params);
+    r->initial_rngs = r->state.rngs;
+  });
+  if (e != VPT_OK) {
+    delete r;
+    return e;
+  }
+  *out = r;
+  return VPT_OK;
+}
+
+void vpth_render_free(vpth_render* render) { delete render; }
+
+int vpth_render_size(const vpth_render* r, int32_t* width, int32_t* height) {
+  if (!r || !width || !height) return VPT_ERR_INVALID;
+  *width = r->state.width, *height = r->state.height;
+  return VPT_OK;
+}
+
+int vpth_render_get_rngs(vpth_render* r, uint64_t* rngs) {
+  if (!r || !rngs) return VPT_ERR_INVALID;
+  return guarded([&] {
+    sync_state(r->state);
+    memcpy(rngs, r->state.rngs.data(), r->state.rngs.size() * sizeof(rng_state));
+  });
+}
+
+int vpth_render_reset(vpth_render* r, uint64_t rng_offset) {
+  if (!r) return VPT_ERR_INVALID;
+  return guarded([&] {
+    r->state.rngs    = r->initial_rngs;
+    r->state.samples = 0;
+    r->state.image.assign(r->state.image.size(), {0, 0, 0, 0});
+    if (auto dstate = device_handle(r->state)) {
+      if (vpt_cuda_reset_state(dstate, (const uint64_t*)r->state.rngs.data()) != VPT_OK)
+        throw std::runtime_error(vpt_cuda_last_error());
+      if (rng_offset && vpt_cuda_advance_rngs(dstate, rng_offset) != VPT_OK)
+        throw std::runtime_error(vpt_cuda_last_error());
+    } else if (rng_offset) {
+      // no device state yet: jump the host copies (same O(log n) recurrence)
+      for (auto& g : r->state.rngs) {
+        uint64_t cur_mult = 6364136223846793005ULL, cur_plus = g.inc, acc_mult = 1, acc_plus = 0;
+        for (auto delta = rng_offset; delta > 0; delta >>= 1) {
+          if (delta & 1) acc_mult *= cur_mult, acc_plus = acc_plus * cur_mult + cur_plus;
+          cur_plus = (cur_mult + 1) * cur_plus, cur_mult *= cur_mult;
+        }
+        g.state = acc_mult * g.state + acc_plus;
+      }
+    }
+  });
+}
+
+int vpth_render_samples(vpth_render* r, int nsamples) {
+  if (!r || nsamples <= 0) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto s = r->owner;
+    if (!s->device) s->device = upload_scene(s->scene, s->bvh, s->lights);
+    bind_device_scene(r->state, s->device, s->scene, s->bvh, s->lights);
+    auto params  = r->params;
+    params.batch = nsamples;
+    pathtrace_samples(r->state, s->scene, s->bvh, s->lights, params);
+  });
+}
+
+int vpth_render_done_samples(const vpth_render* r) { return r ? r->state.samples : 0; }
+
+int vpth_render_get_image(vpth_render* r, float* rgba, int normalized) {
+  if (!r || !rgba) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto n = (size_t)r->state.width * r->state.height;
+    if (normalized) {
+      auto img = get_render(r->state);
+      memcpy(rgba, img.pixels.data(), n * sizeof(vec4f));
+    } else {
+      sync_state(r->state);
+      memcpy(rgba, r->state.image.data(), n * sizeof(vec4f));
+    }
+  });
+}
+
+int vpth_render_stats(const vpth_render* r, vpt_trace_stats* stats) {
+  if (!r || !stats) return VPT_ERR_INVALID;
+  return guarded([&] { *stats = get_trace_stats(r->state); });
+}
+
+void* vpth_render_device_image(vpth_render* r) {
+  if (!r) return nullptr;
+  auto dstate = device_handle(r->state);
+  return dstate ? vpt_cuda_image_device_ptr(dstate) : nullptr;
+}
+
+int vpth_intersect(vpth_scene* s, const float* rays, int n, int instance, int32_t* ids,
+    float* uvd) {
+  if (!s) return VPT_ERR_INVALID;
+  int status = VPT_OK;
+  auto r = guarded([&] {
+    status = vpt_cuda_intersect(device_scene_of(s), rays, n, instance, ids, uvd);
+    if (status != VPT_OK) g_error = vpt_cuda_last_error();
+  });
+  return r != VPT_OK ? r : status;
+}
+
+int vpth_spheretrace(vpth_scene* s, const float* rays, int n, int maxiter, int32_t* ids,
+    float* dn) {
+  if (!s) return VPT_ERR_INVALID;
+  int status = VPT_OK;
+  auto r = guarded([&] {
+    status = vpt_cuda_spheretrace(device_scene_of(s), rays, n, maxiter, ids, dn);
+    if (status != VPT_OK) g_error = vpt_cuda_last_error();
+  });
+  return r != VPT_OK ? r : status;
+}
+
+}  // extern "C"

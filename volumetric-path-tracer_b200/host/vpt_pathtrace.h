@@ -1,0 +1,167 @@
+// vpt_pathtrace.h — the yocto_pathtrace API, served by the B200.
+//
+// Same names, argument meaning, defaults and error behaviour as the
+// reference's public header (libs/yocto_pathtrace/yocto_pathtrace.h:57-139):
+// pathtrace_params, pathtrace_state, pathtrace_lights, the shader enum and its
+// names, make_state / make_bvh / make_lights / tesselate_surfaces /
+// pathtrace_samples / get_render. trace_samples is an alias of
+// pathtrace_samples (the name BASELINE.json uses). The host builds (BVH, light
+// CDFs, per-pixel generators) run on the CPU as in the reference; everything
+// executed per path runs on the GPU through include/vpt_cuda.h. There is no
+// CPU rendering path: without the CUDA library / a device the calls throw.
+#pragma once
+
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "vpt_scene.h"
+
+namespace vpt {
+
+struct rng_state {
+  uint64_t state = 0x853c49e6748fea9bULL;
+  uint64_t inc   = 0xda3e39cb94b95bdbULL;
+};
+
+struct device_binding;  // device-resident mirrors owned by the library
+
+// Rendering state (yocto_pathtrace.h:57-64). image / hits mirror the device
+// accumulation buffers and are refreshed by sync_state() / get_render().
+struct pathtrace_state {
+  int                    width   = 0;
+  int                    height  = 0;
+  int                    samples = 0;
+  std::vector<vec4f>     image   = {};
+  std::vector<int>       hits    = {};
+  std::vector<rng_state> rngs    = {};
+  std::shared_ptr<device_binding> device = {};
+};
+
+// Type of tracing algorithm (order is ABI, yocto_pathtrace.h:74-84)
+enum struct pathtrace_shader_type {
+  volpathtrace, pathtrace, naive, eyelight, normal, texcoord, color, implicit, implicit_normal,
+};
+
+enum struct pathtrace_pipeline { automatic = 0, megakernel = 1, wavefront = 2 };
+
+// Options for trace functions (yocto_pathtrace.h:87-99)
+struct pathtrace_params {
+  int                   camera              = 0;
+  int                   resolution          = 720;
+  pathtrace_shader_type shader              = pathtrace_shader_type::pathtrace;
+  int                   samples             = 512;
+  int                   bounces             = 4;
+  bool                  noparallel          = false;  // accepted, ignored on the GPU
+  int                   pratio              = 8;
+  float                 exposure            = 0;
+  bool                  filmic              = false;
+  bool                  noimplicit_mis      = false;
+  int                   spheretrace_maxiter = 450;
+  // device options (not in the reference)
+  pathtrace_pipeline    pipeline            = pathtrace_pipeline::automatic;
+  int                   batch               = 1;  // samples per pathtrace_samples call
+};
+
+inline const auto pathtrace_shader_names = std::vector<std::string>{"volpathtrace", "pathtrace",
+    "naive", "eyelight", "normal", "texcoord", "color", "implicit", "implicit_normal"};
+
+// Scene lights (yocto_pathtrace.h:106-116)
+struct pathtrace_light {
+  int                instance     = invalidid;
+  int                environment  = invalidid;
+  int                sdf          = invalidid;
+  std::vector<float> elements_cdf = {};
+};
+struct pathtrace_lights {
+  std::vector<pathtrace_light> lights = {};
+};
+
+// Linear float image returned by get_render (image_data, yocto_image.h:68)
+struct color_image {
+  int                width  = 0;
+  int                height = 0;
+  bool               linear = true;
+  std::vector<vec4f> pixels = {};
+};
+
+// Initialize state: image size from the camera aspect and one PCG32 stream per
+// pixel, seeded sequentially from one generator (yocto_pathtrace.cpp:960-980).
+pathtrace_state make_state(const scene_data& scene, const pathtrace_params& params);
+
+// Build the two-level BVH on the host (middle split, <= 4 primitives per leaf;
+// yocto_pathtrace.cpp:955, yocto_bvh.cpp:411-611).
+bvh_scene make_bvh(const scene_data& scene, const pathtrace_params& params);
+bvh_shape make_bvh(const shape_data& shape);
+
+// Light list and sampling CDFs (yocto_pathtrace.cpp:983-1049).
+pathtrace_lights make_lights(const scene_data& scene, const pathtrace_params& params);
+
+// Subdivision surfaces are tessellated by the scene exporter with the
+// reference's own host code before the archive is written; kept for API parity.
+void tesselate_surfaces(scene_data& scene);
+
+// Progressively computes an image: params.batch samples per call (default 1,
+// as the reference). Blocking. Throws std::runtime_error("sampler unknown") for
+// a bad shader and on any CUDA failure.
+void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, const pathtrace_params& params);
+inline void trace_samples(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, const pathtrace_params& params) {
+  pathtrace_samples(state, scene, bvh, lights, params);
+}
+
+// Copies the device accumulation image and generators back into `state`.
+void sync_state(pathtrace_state& state);
+
+// Get resulting render (divides by state.samples, yocto_pathtrace.cpp:1105-1116);
+// the second form throws std::invalid_argument on a size / linearity mismatch.
+color_image get_render(const pathtrace_state& state);
+void        get_render(color_image& render, const pathtrace_state& state);
+
+// The C-ABI scene description (include/vpt_cuda.h) of a host scene; the
+// pointers inside `desc` refer to `scene`, `bvh`, `lights` and to this storage.
+struct scene_desc_storage {
+  std::vector<vpt_camera_desc>          cameras;
+  std::vector<vpt_instance_desc>        instances;
+  std::vector<vpt_shape_desc>           shapes;
+  std::vector<vpt_bvh_desc>             shape_bvhs;
+  std::vector<vpt_material_desc>        materials;
+  std::vector<vpt_texture_desc>         textures;
+  std::vector<vpt_environment_desc>     environments;
+  std::vector<vpt_volume_desc>          volumes;
+  std::vector<vpt_volume_instance_desc> vol_instances;
+  std::vector<vpt_sdf_desc>             sdfs;
+  std::vector<vpt_light_desc>           lights;
+  vpt_scene_desc                        desc{};
+};
+void make_scene_desc(scene_desc_storage& storage, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights);
+
+// Explicit device-scene management, for callers that render the same scene
+// from several states (the first pathtrace_samples call otherwise uploads).
+struct device_scene;
+std::shared_ptr<device_scene> upload_scene(
+    const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
+void bind_device_scene(pathtrace_state& state, const std::shared_ptr<device_scene>& dscene,
+    const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
+vpt_scene* device_handle(const std::shared_ptr<device_scene>& scene);
+vpt_state* device_handle(pathtrace_state& state);
+
+// Device statistics of the last pathtrace_samples call on this state.
+vpt_trace_stats get_trace_stats(const pathtrace_state& state);
+
+// Batched first-hit queries through the device traversal (intersect_bvh,
+// yocto_bvh.cpp:1097-1113). rays: n x {o.xyz, d.xyz, tmin, tmax}.
+struct bvh_intersection {
+  int   instance = -1;
+  int   element  = -1;
+  vec2f uv       = {0, 0};
+  float distance = 0;
+  bool  hit      = false;
+};
+std::vector<bvh_intersection> intersect_bvh(const bvh_scene& bvh, const scene_data& scene,
+    const pathtrace_lights& lights, const std::vector<float>& rays, int instance = -1);
+
+}  // namespace vpt
