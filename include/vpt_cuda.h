@@ -237,6 +237,10 @@ int  vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n);
 int  vpt_cuda_download_rngs(vpt_state* state, uint64_t* rngs, size_t n);
 /* device pointer of the accumulation image, for a collective on the caller's side */
 void* vpt_cuda_image_device_ptr(vpt_state* state);
+/* device-to-device copy of the accumulation image into / from a caller-owned device buffer
+ * (e.g. a torch tensor that takes part in an NCCL reduce); n = width*height*4 floats */
+int  vpt_cuda_export_image(vpt_state* state, void* device_dst, size_t n);
+int  vpt_cuda_import_image(vpt_state* state, const void* device_src, size_t n);
 
 /* first-hit queries for ray batches. rays: [n][8] = o.xyz, d.xyz, tmin, tmax.
  * instance < 0: whole scene; otherwise the instance-targeted variant.

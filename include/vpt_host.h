@@ -52,6 +52,9 @@ int  vpth_render_get_image(vpth_render* render, float* rgba, int normalized);
 int  vpth_render_stats(const vpth_render* render, vpt_trace_stats* stats);
 /* device pointer of the accumulation image (for a collective), or null */
 void* vpth_render_device_image(vpth_render* render);
+/* copy the device accumulation image into / from a caller-owned device buffer */
+int  vpth_render_export_image(vpth_render* render, void* device_dst);
+int  vpth_render_import_image(vpth_render* render, const void* device_src, int total_samples);
 
 int  vpth_intersect(vpth_scene* scene, const float* rays, int n, int instance, int32_t* ids,
          float* uvd);

@@ -12,7 +12,7 @@
 // usage: ref_render <scene.vptscene> <out.vptarch> [--shader NAME]
 //        [--samples N] [--resolution R] [--bounces B] [--noimplicitmis]
 //        [--stmaxiter M] [--noparallel] [--rays rays.vptarch]
-//        [--instance K] [--dump-state]
+//        [--instance K] [--dump-state] [--dump-host]
 #include <yocto/yocto_bvh.h>
 #include <yocto/yocto_scene.h>
 #include <yocto/yocto_sdfs.h>
@@ -51,6 +51,7 @@ int main(int argc, const char** argv) {
   auto rays_file = string{};
   auto instance  = -1;
   auto dump_state = false;
+  auto dump_host  = false;
   for (int i = 3; i < argc; i++) {
     auto a    = string{argv[i]};
     auto next = [&]() -> string {
@@ -90,6 +91,8 @@ int main(int argc, const char** argv) {
       instance = std::stoi(next());
     else if (a == "--dump-state")
       dump_state = true;
+    else if (a == "--dump-host")
+      dump_host = true;
     else {
       fprintf(stderr, "ref_render: unknown option %s\n", a.c_str());
       return 2;
@@ -110,7 +113,32 @@ int main(int argc, const char** argv) {
   auto out = vpt::archive{};
   auto bvh = make_bvh(scene, params);
 
-  if (!rays_file.empty()) {
+  if (dump_host) {
+    // host-built structures of the reference: bvh nodes / primitives (make_bvh,
+    // yocto_bvh.cpp:574), light list + cdfs (make_lights, yocto_pathtrace.cpp:983)
+    // and the initial per-pixel generators (make_state, :960)
+    static_assert(sizeof(bvh_node) == 32, "bvh_node layout");
+    auto put_bvh = [&](const string& pre, const bvh_data& b) {
+      out.add(pre + "nodes", vpt::dt_u8, {(uint64_t)b.nodes.size(), 32}, b.nodes.data());
+      out.add_i32(pre + "prims", {(uint64_t)b.primitives.size()}, b.primitives.data());
+    };
+    put_bvh("bvh.scene.", bvh);
+    for (size_t i = 0; i < bvh.shapes.size(); i++)
+      put_bvh("bvh.shape" + std::to_string(i) + ".", bvh.shapes[i]);
+    auto lights = make_lights(scene, params);
+    auto ids    = vector<int>(lights.lights.size() * 3);
+    for (size_t i = 0; i < lights.lights.size(); i++) {
+      auto& l        = lights.lights[i];
+      ids[i * 3 + 0] = l.instance, ids[i * 3 + 1] = l.environment, ids[i * 3 + 2] = l.sdf;
+      out.add_f32("lights.cdf" + std::to_string(i), {(uint64_t)l.elements_cdf.size()},
+          l.elements_cdf.data());
+    }
+    out.add_i32("lights.ids", {(uint64_t)lights.lights.size(), 3}, ids.data());
+    auto state = make_state(scene, params);
+    int  wh[2] = {state.width, state.height};
+    out.add_i32("state.size", {2}, wh);
+    out.add("state.rngs", vpt::dt_u64, {(uint64_t)state.rngs.size(), 2}, state.rngs.data());
+  } else if (!rays_file.empty()) {
     auto ra = vpt::archive{};
     if (!ra.load(rays_file, error)) {
       fprintf(stderr, "ref_render: %s\n", error.c_str());

@@ -12,6 +12,7 @@
 //        [--resolution R] [--bounces B] [--noimplicitmis] [--stmaxiter M]
 //        [--rays rays.vptarch] [--instance K] [--threads T]
 #define VPT_HOST_POOL 1
+#define VPT_STACK_CHECK 1
 #include <chrono>
 #include <thread>
 
@@ -159,6 +160,8 @@ int main(int argc, const char** argv) {
     printf("hostsim: %dx%d %d spp shader=%s %.3f s\n", state.width, state.height, params.samples,
         pathtrace_shader_names[(int)params.shader].c_str(), seconds);
   }
+  printf("hostsim: traversal stack high water %d entries, uploader bound %d\n",
+      vpt_stack_high_water + 1, flat.stack_depth);
   if (!out.save(argv[2], error)) return 1;
   return 0;
 }

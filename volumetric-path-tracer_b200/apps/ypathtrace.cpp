@@ -1,0 +1,231 @@
+// ypathtrace — offline command line of the B200 path tracer.
+//
+// Mirrors run() / run_offline() of the reference CLI
+// (apps/ypathtrace/ypathtrace.cpp:41-87, :307-341): same flags, defaults and
+// call sequence (load_scene -> tesselate_surfaces -> make_bvh -> make_lights ->
+// make_state -> pathtrace_samples x N -> get_render -> save_image). Differences:
+// the scene is a ".vptscene" archive (asset loading stays with the reference's
+// loaders, see oracle/tools/vpt_export.cpp); --interactive is unavailable on
+// this box (no OpenGL); the image writers are .hdr / .pfm / .ppm / .png.
+// Added flags: --pipeline {auto,mega,wavefront}, --batch N, --device K.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "vpt_pathtrace.h"
+
+using namespace vpt;
+
+static void print_fatal(const std::string& msg) {
+  printf("\n%s\n", msg.c_str());
+  exit(1);
+}
+
+static float rgb_to_srgb(float rgb) {
+  return (rgb <= 0.0031308f) ? 12.92f * rgb : (1 + 0.055f) * std::pow(rgb, 1 / 2.4f) - 0.055f;
+}
+static uint8_t float_to_byte(float a) {
+  auto v = (int)(a * 256);
+  return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v));
+}
+
+static uint32_t crc32_of(const uint8_t* data, size_t n, uint32_t crc = 0) {
+  static uint32_t table[256];
+  if (!table[1])
+    for (uint32_t i = 0; i < 256; i++) {
+      auto c = i;
+      for (int k = 0; k < 8; k++) c = (c & 1) ? 0xedb88320u ^ (c >> 1) : c >> 1;
+      table[i] = c;
+    }
+  crc = ~crc;
+  for (size_t i = 0; i < n; i++) crc = table[(crc ^ data[i]) & 255] ^ (crc >> 8);
+  return ~crc;
+}
+
+// PNG with stored (uncompressed) deflate blocks: no zlib dependency
+static bool save_png(const std::string& path, int w, int h, const std::vector<uint8_t>& rgba) {
+  auto raw = std::vector<uint8_t>{};
+  for (int j = 0; j < h; j++) {
+    raw.push_back(0);
+    raw.insert(raw.end(), rgba.begin() + (size_t)j * w * 4, rgba.begin() + (size_t)(j + 1) * w * 4);
+  }
+  auto z = std::vector<uint8_t>{0x78, 0x01};
+  uint32_t a = 1, b = 0;
+  for (auto v : raw) a = (a + v) % 65521, b = (b + a) % 65521;
+  for (size_t pos = 0; pos < raw.size();) {
+    auto n = std::min<size_t>(65535, raw.size() - pos);
+    z.push_back(pos + n == raw.size() ? 1 : 0);
+    z.push_back(n & 255), z.push_back(n >> 8), z.push_back(~n & 255), z.push_back((~n >> 8) & 255);
+    z.insert(z.end(), raw.begin() + pos, raw.begin() + pos + n);
+    pos += n;
+  }
+  uint32_t adler = (b << 16) | a;
+  for (int k = 3; k >= 0; k--) z.push_back((adler >> (8 * k)) & 255);
+  auto fs = fopen(path.c_str(), "wb");
+  if (!fs) return false;
+  auto chunk = [&](const char* tag, const std::vector<uint8_t>& data) {
+    auto buf = std::vector<uint8_t>(tag, tag + 4);
+    buf.insert(buf.end(), data.begin(), data.end());
+    uint32_t len = (uint32_t)data.size(), crc = crc32_of(buf.data(), buf.size());
+    uint8_t  be[4] = {(uint8_t)(len >> 24), (uint8_t)(len >> 16), (uint8_t)(len >> 8), (uint8_t)len};
+    fwrite(be, 1, 4, fs);
+    fwrite(buf.data(), 1, buf.size(), fs);
+    uint8_t ce[4] = {(uint8_t)(crc >> 24), (uint8_t)(crc >> 16), (uint8_t)(crc >> 8), (uint8_t)crc};
+    fwrite(ce, 1, 4, fs);
+  };
+  fwrite("\x89PNG\r\n\x1a\n", 1, 8, fs);
+  auto ihdr = std::vector<uint8_t>{(uint8_t)(w >> 24), (uint8_t)(w >> 16), (uint8_t)(w >> 8),
+      (uint8_t)w, (uint8_t)(h >> 24), (uint8_t)(h >> 16), (uint8_t)(h >> 8), (uint8_t)h, 8, 6, 0,
+      0, 0};
+  chunk("IHDR", ihdr), chunk("IDAT", z), chunk("IEND", {});
+  fclose(fs);
+  return true;
+}
+
+// save_image by extension (yocto_sceneio.cpp:509-591): ldr formats get rgb_to_srgb + 8 bit
+static bool save_image(const std::string& path, const color_image& image, std::string& error) {
+  auto ext = path.substr(path.find_last_of('.') == std::string::npos ? path.size()
+                                                                      : path.find_last_of('.'));
+  auto w = image.width, h = image.height;
+  if (ext == ".hdr" || ext == ".pfm") {
+    auto fs = fopen(path.c_str(), "wb");
+    if (!fs) return error = "cannot create " + path, false;
+    if (ext == ".pfm") {
+      fprintf(fs, "PF\n%d %d\n-1.0\n", w, h);
+      for (int j = h - 1; j >= 0; j--)
+        for (int i = 0; i < w; i++) fwrite(&image.pixels[(size_t)j * w + i], 4, 3, fs);
+    } else {
+      fprintf(fs, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n", h, w);
+      for (auto& p : image.pixels) {
+        auto    m = std::fmax(p.x, std::fmax(p.y, p.z));
+        uint8_t rgbe[4] = {0, 0, 0, 0};
+        if (m > 1e-32f) {
+          int  e;
+          auto s  = std::frexp(m, &e) * 256.0f / m;
+          rgbe[0] = (uint8_t)(p.x * s), rgbe[1] = (uint8_t)(p.y * s), rgbe[2] = (uint8_t)(p.z * s);
+          rgbe[3] = (uint8_t)(e + 128);
+        }
+        fwrite(rgbe, 1, 4, fs);
+      }
+    }
+    fclose(fs);
+    return true;
+  }
+  auto bytes = std::vector<uint8_t>((size_t)w * h * 4);
+  for (size_t i = 0; i < (size_t)w * h; i++) {
+    auto& p          = image.pixels[i];
+    bytes[4 * i + 0] = float_to_byte(rgb_to_srgb(p.x));
+    bytes[4 * i + 1] = float_to_byte(rgb_to_srgb(p.y));
+    bytes[4 * i + 2] = float_to_byte(rgb_to_srgb(p.z));
+    bytes[4 * i + 3] = float_to_byte(p.w);
+  }
+  if (ext == ".png") {
+    if (!save_png(path, w, h, bytes)) return error = "cannot create " + path, false;
+    return true;
+  }
+  if (ext == ".ppm") {
+    auto fs = fopen(path.c_str(), "wb");
+    if (!fs) return error = "cannot create " + path, false;
+    fprintf(fs, "P6\n%d %d\n255\n", w, h);
+    for (size_t i = 0; i < (size_t)w * h; i++) fwrite(&bytes[4 * i], 1, 3, fs);
+    fclose(fs);
+    return true;
+  }
+  error = "unsupported image format " + ext + " (use .png, .ppm, .hdr or .pfm)";
+  return false;
+}
+
+int main(int argc, const char** argv) {
+  auto scenename   = std::string{"scene.vptscene"};
+  auto outname     = std::string{"out.png"};
+  auto interactive = false;
+  auto device      = 0;
+  auto params      = pathtrace_params{};
+  params.batch     = 16;
+  auto usage       = [&]() {
+    printf("usage: ypathtrace [--scene S.vptscene] [--output IMG] [--interactive]\n"
+           "  [--resolution 1..4096] [--shader NAME] [--samples 1..4096] [--bounces 1..128]\n"
+           "  [--noparallel] [--noimplicitmis] [--stmaxiter 1..512]\n"
+           "  [--pipeline auto|mega|wavefront] [--batch N] [--device K]\n  shaders:");
+    for (auto& n : pathtrace_shader_names) printf(" %s", n.c_str());
+    printf("\n");
+  };
+  auto ranged = [&](const char* name, const std::string& v, int lo, int hi) {
+    auto x = std::stoi(v);
+    if (x < lo || x > hi) print_fatal(std::string("bad value for ") + name);
+    return x;
+  };
+  for (int i = 1; i < argc; i++) {
+    auto a    = std::string{argv[i]};
+    auto next = [&]() -> std::string {
+      if (i + 1 >= argc) print_fatal("missing value for " + a);
+      return argv[++i];
+    };
+    if (a == "--scene") scenename = next();
+    else if (a == "--output") outname = next();
+    else if (a == "--interactive") interactive = true;
+    else if (a == "--resolution") params.resolution = ranged("resolution", next(), 1, 4096);
+    else if (a == "--samples") params.samples = ranged("samples", next(), 1, 4096);
+    else if (a == "--bounces") params.bounces = ranged("bounces", next(), 1, 128);
+    else if (a == "--stmaxiter") params.spheretrace_maxiter = ranged("stmaxiter", next(), 1, 512);
+    else if (a == "--noparallel") params.noparallel = true;
+    else if (a == "--noimplicitmis") params.noimplicit_mis = true;
+    else if (a == "--batch") params.batch = ranged("batch", next(), 1, 4096);
+    else if (a == "--device") device = std::stoi(next());
+    else if (a == "--shader") {
+      auto name = next(), found = std::string{};
+      for (size_t k = 0; k < pathtrace_shader_names.size(); k++)
+        if (pathtrace_shader_names[k] == name) params.shader = (pathtrace_shader_type)k, found = name;
+      if (found.empty()) print_fatal("unknown shader " + name);
+    } else if (a == "--pipeline") {
+      auto name = next();
+      if (name == "auto") params.pipeline = pathtrace_pipeline::automatic;
+      else if (name == "mega") params.pipeline = pathtrace_pipeline::megakernel;
+      else if (name == "wavefront") params.pipeline = pathtrace_pipeline::wavefront;
+      else print_fatal("unknown pipeline " + name);
+    } else if (a == "--help" || a == "-h") {
+      usage();
+      return 0;
+    } else {
+      usage();
+      print_fatal("unknown option " + a);
+    }
+  }
+  if (interactive) print_fatal("interactive view unavailable on this box (no OpenGL)");
+
+  try {
+    auto clock = [] { return std::chrono::steady_clock::now(); };
+    auto since = [&](auto t0) { return std::chrono::duration<double>(clock() - t0).count(); };
+    if (vpt_cuda_set_device(device) != VPT_OK) print_fatal(vpt_cuda_last_error());
+    auto t0    = clock();
+    auto error = std::string{};
+    auto scene = scene_data{};
+    if (!load_scene(scenename, scene, error)) print_fatal(error);
+    printf("load scene: %.3f s\n", since(t0));
+    tesselate_surfaces(scene);
+    t0       = clock();
+    auto bvh = make_bvh(scene, params);
+    printf("build bvh: %.3f s\n", since(t0));
+    t0          = clock();
+    auto lights = make_lights(scene, params);
+    printf("build lights: %.3f s\n", since(t0));
+    auto state = make_state(scene, params);
+    t0         = clock();
+    while (state.samples < params.samples) {
+      pathtrace_samples(state, scene, bvh, lights, params);
+      printf("\rrender samples: %d/%d", state.samples, params.samples);
+      fflush(stdout);
+    }
+    auto render  = get_render(state);
+    auto seconds = since(t0);
+    printf("\nrender: %.3f s, %.2f Mpaths/s (%dx%d, %d spp, %s)\n", seconds,
+        (double)state.width * state.height * state.samples / seconds / 1e6, state.width,
+        state.height, state.samples, pathtrace_shader_names[(int)params.shader].c_str());
+    if (!save_image(outname, render, error)) print_fatal(error);
+    printf("saved %s\n", outname.c_str());
+  } catch (std::exception& e) {
+    print_fatal(e.what());
+  }
+  return 0;
+}

@@ -22,11 +22,19 @@ namespace vpt {
 // Per-thread traversal stack. On the device it is a column of a shared-memory
 // array (stride = threads per block, so lanes hit distinct banks); the host
 // build of this header uses a plain array.
+#if defined(VPT_STACK_CHECK)
+inline int vpt_stack_high_water = -1;  // tests/hostsim only
+#endif
 struct stack_t {
   int* base;
   int  stride;
   VPT_FN int  get(int i) const { return base[i * stride]; }
-  VPT_FN void set(int i, int v) const { base[i * stride] = v; }
+  VPT_FN void set(int i, int v) const {
+#if defined(VPT_STACK_CHECK)
+    if (i > vpt_stack_high_water) vpt_stack_high_water = i;
+#endif
+    base[i * stride] = v;
+  }
 };
 
 constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
@@ -83,63 +91,64 @@ VPT_FN bool intersect_quad(f3 o, f3 d, float tmin, float tmax, f3 p0, f3 p1, f3 
 }
 
 // Shape-level walk in instance space; uses stack slots [base, ...).
-VPT_FN bool intersect_shape(const DScene& sc, int root, int kind, f3 o, f3 d, float tmin,
+#if defined(VPT_NOINLINE_TRAVERSAL)
+VPT_NOINLINE
+#else
+VPT_FN
+#endif
+bool intersect_shape(const DScene& sc, int root, int kind, f3 o, f3 d, float tmin,
     float tmax, stack_t st, int base, int& element, f2& uv, float& distance) {
   if (root < 0) return false;
   auto hit  = false;
   auto dinv = f3{1 / d.x, 1 / d.y, 1 / d.z};
   int  neg[3] = {dinv.x < 0 ? 1 : 0, dinv.y < 0 ? 1 : 0, dinv.z < 0 ? 1 : 0};
-  int  cur  = base;
-  int  next = root;
-  while (true) {
-    int ni;
-    if (next >= 0) {
-      ni   = next;
-      next = -1;
-    } else {
-      if (cur == base) break;
-      ni = st.get(--cur);
-    }
+  // single-exit loop: push root, pop until the stack is back at `base`
+  int cur = base;
+  st.set(cur++, root);
+  VPT_GUARD_DECL(guard);
+  while (cur != base) {
+    VPT_GUARD_STEP(1, guard, 30000);
+    int  ni = st.get(--cur);
     auto n0 = ld4(sc.nodes + 2 * ni), n1 = ld4(sc.nodes + 2 * ni + 1);
-    if (!intersect_box(o, dinv, tmin, tmax, n0, n1)) continue;
-    auto start = f2i(n1.z), meta = f2i(n1.w);
-    if (meta >> 24) {
-      auto axis = (meta >> 16) & 3;
-      auto sgn  = axis == 0 ? neg[0] : (axis == 1 ? neg[1] : neg[2]);
-      // reference pushes (c0, c1) if the sign is set, (c1, c0) otherwise, then
-      // pops the last pushed: keep that one in `next`.
-      if (sgn) {
-        st.set(cur++, start + 0);
-        next = start + 1;
+    if (intersect_box(o, dinv, tmin, tmax, n0, n1)) {
+      auto start = f2i(n1.z), meta = f2i(n1.w);
+      if (meta >> 24) {
+        auto axis = (meta >> 16) & 3;
+        auto sgn  = axis == 0 ? neg[0] : (axis == 1 ? neg[1] : neg[2]);
+        // reference order: push (c0, c1) if the sign is set, else (c1, c0); the
+        // last pushed child is visited first
+        st.set(cur++, sgn ? start : start + 1);
+        st.set(cur++, sgn ? start + 1 : start);
       } else {
-        st.set(cur++, start + 1);
-        next = start + 0;
-      }
-    } else {
-      auto num = meta & 0xffff;
-      if (kind == kind_quads) {
-        for (auto i = 0; i < num; i++) {
-          auto p = sc.prims + start + 4 * i;
-          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), e = ld4(p + 3);
-          if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(e), uv, distance)) {
-            hit     = true;
-            element = f2i(a.w);
-            tmax    = distance;
+        auto num = meta & 0xffff;
+        if (kind == kind_quads) {
+          for (auto i = 0; i < num; i++) {
+            auto p = sc.prims + start + 4 * i;
+            auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), e = ld4(p + 3);
+            if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(e), uv, distance)) {
+              hit     = true;
+              element = f2i(a.w);
+              tmax    = distance;
+            }
           }
-        }
-      } else {
-        for (auto i = 0; i < num; i++) {
-          auto p = sc.prims + start + 3 * i;
-          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
-          if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), uv, distance)) {
-            hit     = true;
-            element = f2i(a.w);
-            tmax    = distance;
+        } else {
+          for (auto i = 0; i < num; i++) {
+            auto p = sc.prims + start + 3 * i;
+            auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
+            if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), uv, distance)) {
+              hit     = true;
+              element = f2i(a.w);
+              tmax    = distance;
+            }
           }
         }
       }
     }
   }
+#if defined(VPT_GUARD) && defined(__CUDA_ARCH__)
+  VPT_COUNT_ADD(5, guard >> 4);
+  VPT_COUNT_MAX(8, guard);
+#endif
   return hit;
 }
 
@@ -165,44 +174,35 @@ VPT_FN hit_t intersect_scene(const DScene& sc, const ray3& ray, stack_t st) {
   auto tmin = ray.tmin, tmax = ray.tmax;
   auto dinv = f3{1 / d.x, 1 / d.y, 1 / d.z};
   int  neg[3] = {dinv.x < 0 ? 1 : 0, dinv.y < 0 ? 1 : 0, dinv.z < 0 ? 1 : 0};
-  int  cur  = 0;
-  int  next = sc.scene_root;
-  while (true) {
-    int ni;
-    if (next >= 0) {
-      ni   = next;
-      next = -1;
-    } else {
-      if (cur == 0) break;
-      ni = st.get(--cur);
-    }
+  int cur = 0;
+  st.set(cur++, sc.scene_root);
+  VPT_GUARD_DECL(guard);
+  while (cur != 0) {
+    VPT_GUARD_STEP(2, guard, 30000);
+    int  ni = st.get(--cur);
     auto n0 = ld4(sc.nodes + 2 * ni), n1 = ld4(sc.nodes + 2 * ni + 1);
-    if (!intersect_box(o, dinv, tmin, tmax, n0, n1)) continue;
-    auto start = f2i(n1.z), meta = f2i(n1.w);
-    if (meta >> 24) {
-      auto axis = (meta >> 16) & 3;
-      auto sgn  = axis == 0 ? neg[0] : (axis == 1 ? neg[1] : neg[2]);
-      if (sgn) {
-        st.set(cur++, start + 0);
-        next = start + 1;
+    if (intersect_box(o, dinv, tmin, tmax, n0, n1)) {
+      auto start = f2i(n1.z), meta = f2i(n1.w);
+      if (meta >> 24) {
+        auto axis = (meta >> 16) & 3;
+        auto sgn  = axis == 0 ? neg[0] : (axis == 1 ? neg[1] : neg[2]);
+        st.set(cur++, sgn ? start : start + 1);
+        st.set(cur++, sgn ? start + 1 : start);
       } else {
-        st.set(cur++, start + 1);
-        next = start + 0;
-      }
-    } else {
-      auto num = meta & 0xffff;
-      for (auto i = 0; i < num; i++) {
-        auto inst = ld1(sc.scene_prims + start + i);
-        auto t    = sc.inst_trav + 4 * inst;
-        auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
-        auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
-        auto io  = transform_point(inv, o);
-        auto id  = transform_vector(inv, d);
-        if (intersect_shape(sc, f2i(c0.w), f2i(c1.w), io, id, tmin, tmax, st, cur, h.element,
-                h.uv, h.distance)) {
-          h.hit      = true;
-          h.instance = inst;
-          tmax       = h.distance;
+        auto num = meta & 0xffff;
+        for (auto i = 0; i < num; i++) {
+          auto inst = ld1(sc.scene_prims + start + i);
+          auto t    = sc.inst_trav + 4 * inst;
+          auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
+          auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
+          auto io  = transform_point(inv, o);
+          auto id  = transform_vector(inv, d);
+          if (intersect_shape(sc, f2i(c0.w), f2i(c1.w), io, id, tmin, tmax, st, cur, h.element,
+                  h.uv, h.distance)) {
+            h.hit      = true;
+            h.instance = inst;
+            tmax       = h.distance;
+          }
         }
       }
     }

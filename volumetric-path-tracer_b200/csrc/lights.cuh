@@ -18,7 +18,9 @@ VPT_FN int sample_discrete(const float* cdf, int n, float r) {
   auto last = ld1(cdf + n - 1);
   r         = vclamp(r * last, (float)0, last - (float)0.00001);
   int first = 0, len = n;
+  VPT_GUARD_DECL(guard);
   while (len > 0) {
+    VPT_GUARD_STEP(4, guard, 64);
     auto half = len >> 1;
     auto mid  = first + half;
     if (r < ld1(cdf + mid)) {
@@ -92,6 +94,8 @@ VPT_FN float sample_lights_pdf(const DScene& sc, f3 position, f3 direction,
         auto lnormal   = eval_element_normal(sc, in, isec.element);
         lpdf += distance_squared(lposition, position) / (vabs(dot(lnormal, direction)) * area);
         next_position = lposition + direction * 1e-3f;
+        VPT_COUNT_ADD(6, 1);
+        VPT_COUNT_MAX(9, bounce);
       }
       pdf += lpdf;
     } else if (l0.z != invalidid) {

@@ -336,18 +336,23 @@ VPT_FN f4 shade_path(const DScene& sc, const DParams& prm, const ray3& ray, rng_
   if (S == shader_implicit_normal) return shade_implicit_normal(sc, prm, ray);
   path_t p;
   path_init(p, ray);
-  auto maxb = max_bounces<S>(prm);
-  while (p.bounce < maxb) {
+  // single-exit loop: `alive` is the only way out
+  auto alive = p.bounce < max_bounces<S>(prm);
+  VPT_GUARD_DECL(guard);
+  while (alive) {
+    VPT_GUARD_STEP(3, guard, 1000);
     auto      isec = find_hit<S>(sc, prm, p, st);
     pending_t pd;
     auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);
-    if (r == step_done) break;
-    if (r == step_skip) continue;
     if (r == step_lightpdf) {
       auto lpdf = sample_lights_pdf(sc, pd.position, pd.incoming, prm.spheretrace_maxiter, st);
       apply_lightpdf(p, pd, lpdf);
     }
-    if (!bounce_tail<S>(prm, p, rng)) break;
+    if (r == step_done) {
+      alive = false;
+    } else if (r != step_skip) {
+      alive = bounce_tail<S>(prm, p, rng);
+    }
   }
   return path_result(S, p);
 }

@@ -23,6 +23,27 @@
 #define VPT_NOINLINE inline
 #endif
 
+// Debug-only loop guards (build with -DVPT_GUARD): a loop that exceeds its bound
+// records its id and breaks, so a hang can be localised from the host.
+#if defined(VPT_GUARD) && defined(__CUDACC__)
+__device__ int vpt_guard_flags[16];
+#endif
+#if defined(VPT_GUARD) && defined(__CUDA_ARCH__)
+#define VPT_GUARD_DECL(name) int name = 0
+#define VPT_GUARD_STEP(id, name, limit) \
+  if (++name > (limit)) {               \
+    vpt_guard_flags[id] = name;         \
+    break;                              \
+  }
+#define VPT_COUNT_ADD(id, v) atomicAdd(&vpt_guard_flags[id], (int)(v))
+#define VPT_COUNT_MAX(id, v) atomicMax(&vpt_guard_flags[id], (int)(v))
+#else
+#define VPT_GUARD_DECL(name)
+#define VPT_GUARD_STEP(id, name, limit)
+#define VPT_COUNT_ADD(id, v)
+#define VPT_COUNT_MAX(id, v)
+#endif
+
 namespace vpt {
 
 constexpr float pif     = 3.14159265358979323846f;

@@ -199,6 +199,16 @@ static cudaError_t dispatch_mega(const vpt_scene* scene, vpt_state* state, const
 // ---------------------------------------------------------------------------
 extern "C" {
 
+// debug builds only (-DVPT_GUARD): loop-guard flags, zeros otherwise
+int vpt_cuda_debug_flags(int32_t out[16]) {
+  for (int i = 0; i < 16; i++) out[i] = 0;
+#if defined(VPT_GUARD)
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, vpt_guard_flags, sizeof(int) * 16);
+#endif
+  return VPT_OK;
+}
+
 int vpt_cuda_device_count(void) {
   int  n = 0;
   auto e = cudaGetDeviceCount(&n);
@@ -374,6 +384,22 @@ int vpt_cuda_download_rngs(vpt_state* state, uint64_t* rngs, size_t n) {
 }
 
 void* vpt_cuda_image_device_ptr(vpt_state* state) { return state ? state->image : nullptr; }
+
+int vpt_cuda_export_image(vpt_state* state, void* device_dst, size_t n) {
+  if (!state || !device_dst) return set_error(VPT_ERR_INVALID, "null argument");
+  size_t want = (size_t)state->width * state->height * 4;
+  if (n != want) return set_error(VPT_ERR_INVALID, "image should have the same size");
+  VPT_CUDA_TRY(cudaMemcpy(device_dst, state->image, want * sizeof(float), cudaMemcpyDeviceToDevice));
+  return VPT_OK;
+}
+
+int vpt_cuda_import_image(vpt_state* state, const void* device_src, size_t n) {
+  if (!state || !device_src) return set_error(VPT_ERR_INVALID, "null argument");
+  size_t want = (size_t)state->width * state->height * 4;
+  if (n != want) return set_error(VPT_ERR_INVALID, "image should have the same size");
+  VPT_CUDA_TRY(cudaMemcpy(state->image, device_src, want * sizeof(float), cudaMemcpyDeviceToDevice));
+  return VPT_OK;
+}
 
 int vpt_cuda_intersect(vpt_scene* scene, const float* rays, int n, int instance, int32_t* ids,
     float* uvd) {

@@ -238,6 +238,30 @@ void* vpth_render_device_image(vpth_render* r) {
   return dstate ? vpt_cuda_image_device_ptr(dstate) : nullptr;
 }
 
+int vpth_render_export_image(vpth_render* r, void* device_dst) {
+  if (!r) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto dstate = device_handle(r->state);
+    if (!dstate) throw std::invalid_argument("nothing rendered yet");
+    auto n = (size_t)r->state.width * r->state.height * 4;
+    if (vpt_cuda_export_image(dstate, device_dst, n) != VPT_OK)
+      throw std::runtime_error(vpt_cuda_last_error());
+  });
+}
+
+// after a cross-GPU reduce: the summed image and the total sample count come back
+int vpth_render_import_image(vpth_render* r, const void* device_src, int total_samples) {
+  if (!r) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto dstate = device_handle(r->state);
+    if (!dstate) throw std::invalid_argument("nothing rendered yet");
+    auto n = (size_t)r->state.width * r->state.height * 4;
+    if (vpt_cuda_import_image(dstate, device_src, n) != VPT_OK)
+      throw std::runtime_error(vpt_cuda_last_error());
+    mark_device_dirty(r->state, total_samples);
+  });
+}
+
 int vpth_intersect(vpth_scene* s, const float* rays, int n, int instance, int32_t* ids,
     float* uvd) {
   if (!s) return VPT_ERR_INVALID;

@@ -293,6 +293,12 @@ vpt_state* device_handle(pathtrace_state& state) {
   return state.device ? state.device->state : nullptr;
 }
 
+void mark_device_dirty(pathtrace_state& state, int samples) {
+  if (!state.device) return;
+  state.device->dirty = true;
+  state.samples       = samples;
+}
+
 static vpt_params to_c_params(const pathtrace_params& p) {
   auto c = vpt_params{};
   c.camera = p.camera, c.resolution = p.resolution, c.shader = (int)p.shader;

@@ -148,6 +148,9 @@ void bind_device_scene(pathtrace_state& state, const std::shared_ptr<device_scen
     const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
 vpt_scene* device_handle(const std::shared_ptr<device_scene>& scene);
 vpt_state* device_handle(pathtrace_state& state);
+// the device image was replaced (e.g. by a cross-GPU reduce): state.samples becomes
+// `samples` and the host mirror is refreshed on the next sync_state / get_render
+void mark_device_dirty(pathtrace_state& state, int samples);
 
 // Device statistics of the last pathtrace_samples call on this state.
 vpt_trace_stats get_trace_stats(const pathtrace_state& state);
