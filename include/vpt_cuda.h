@@ -214,6 +214,10 @@ int  vpt_cuda_device_count(void);
 int  vpt_cuda_set_device(int device);
 const char* vpt_cuda_last_error(void);
 
+/* page-lock caller-owned host buffers so uploads / downloads run at full PCIe rate */
+int  vpt_cuda_host_register(void* ptr, size_t bytes);
+int  vpt_cuda_host_unregister(void* ptr);
+
 int  vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out);
 void vpt_cuda_free_scene(vpt_scene* scene);
 size_t vpt_cuda_scene_bytes(const vpt_scene* scene);

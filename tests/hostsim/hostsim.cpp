@@ -13,6 +13,7 @@
 //        [--rays rays.vptarch] [--instance K] [--threads T]
 #define VPT_HOST_POOL 1
 #define VPT_STACK_CHECK 1
+#define VPT_WORK_COUNTERS 1
 #include <chrono>
 #include <thread>
 
@@ -157,6 +158,25 @@ int main(int argc, const char** argv) {
     int meta[4] = {state.width, state.height, params.samples, nthreads};
     out.add_i32("meta", {4}, meta);
     out.add_f32("seconds", {1}, &seconds);
+    {
+      // algorithmic work per camera path (feeds bench.py's roofline)
+      double paths = (double)state.width * state.height * params.samples;
+      long long v[12] = {g_work.box_tests, g_work.tri_tests, g_work.inst_transforms,
+          g_work.scene_queries, g_work.instance_queries, g_work.sdf_scene_evals,
+          g_work.sdf_fn_evals, g_work.sdf_grid_evals, g_work.trilinear, g_work.bounces,
+          g_work.lightpdf_calls, g_work.texel_reads};
+      const char* names[12] = {"box_tests", "tri_tests", "inst_transforms", "scene_queries",
+          "instance_queries", "sdf_scene_evals", "sdf_fn_evals", "sdf_grid_evals", "trilinear",
+          "bounces", "lightpdf_calls", "texel_reads"};
+      float per_path[12];
+      printf("hostsim work per path:");
+      for (int i = 0; i < 12; i++) {
+        per_path[i] = (float)(v[i] / paths);
+        printf(" %s=%.3f", names[i], per_path[i]);
+      }
+      printf("\n");
+      out.add_f32("work_per_path", {12}, per_path);
+    }
     printf("hostsim: %dx%d %d spp shader=%s %.3f s\n", state.width, state.height, params.samples,
         pathtrace_shader_names[(int)params.shader].c_str(), seconds);
   }

@@ -40,6 +40,7 @@ struct stack_t {
 constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
 
 VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1) {
+  VPT_WORK(box_tests, 1);
   auto bmin   = f3{n0.x, n0.y, n0.z};
   auto bmax   = f3{n0.w, n1.x, n1.y};
   auto it_min = (bmin - o) * dinv;
@@ -55,6 +56,7 @@ VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1) {
 // Moller-Trumbore, two-sided (yocto_geometry.h:786-819)
 VPT_FN bool intersect_triangle(f3 o, f3 d, float tmin, float tmax, f3 p0, f3 p1, f3 p2,
     f2& uv, float& dist) {
+  VPT_WORK(tri_tests, 1);
   auto edge1 = p1 - p0;
   auto edge2 = p2 - p0;
   auto pvec  = cross(d, edge2);
@@ -156,6 +158,8 @@ bool intersect_shape(const DScene& sc, int root, int kind, f3 o, f3 d, float tmi
 VPT_FN hit_t intersect_instance(
     const DScene& sc, int instance, const ray3& ray, stack_t st, int base = 0) {
   auto h  = hit_t{instance, -1, {0, 0}, 0, false};
+  VPT_WORK(instance_queries, 1);
+  VPT_WORK(inst_transforms, 1);
   auto t  = sc.inst_trav + 4 * instance;
   auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
   auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
@@ -169,6 +173,7 @@ VPT_FN hit_t intersect_instance(
 // Closest hit over the whole scene (yocto_bvh.cpp:800-871).
 VPT_FN hit_t intersect_scene(const DScene& sc, const ray3& ray, stack_t st) {
   auto h = hit_t{-1, -1, {0, 0}, 0, false};
+  VPT_WORK(scene_queries, 1);
   if (sc.scene_root < 0) return h;
   auto o = ray.o, d = ray.d;
   auto tmin = ray.tmin, tmax = ray.tmax;
@@ -192,6 +197,7 @@ VPT_FN hit_t intersect_scene(const DScene& sc, const ray3& ray, stack_t st) {
         auto num = meta & 0xffff;
         for (auto i = 0; i < num; i++) {
           auto inst = ld1(sc.scene_prims + start + i);
+          VPT_WORK(inst_transforms, 1);
           auto t    = sc.inst_trav + 4 * inst;
           auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
           auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};

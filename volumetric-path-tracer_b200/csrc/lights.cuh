@@ -79,6 +79,7 @@ VPT_FN f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2 r
 VPT_FN float sample_lights_pdf(const DScene& sc, f3 position, f3 direction,
     int spheretrace_maxiter, stack_t st, unsigned long long* ray_counter = nullptr) {
   auto pdf = 0.0f;
+  VPT_WORK(lightpdf_calls, 1);
   for (auto li = 0; li < sc.num_lights; li++) {
     auto l0 = ld4(sc.lights + 2 * li), l1 = ld4(sc.lights + 2 * li + 1);
     if (l0.x != invalidid) {

@@ -42,6 +42,7 @@ VPT_FN float srgb_to_rgb1(float srgb) {
 }
 
 VPT_FN f4 lookup_texture(const DScene& sc, i4 tex, int i, int j, bool as_linear) {
+  VPT_WORK(texel_reads, 1);
   auto idx    = tex.w + j * tex.x + i;
   auto decode = as_linear && !(tex.z & 1);
   if (tex.z & 2) {

@@ -54,6 +54,7 @@ VPT_FN sdf_fn ld_sdf(const DScene& sc, int id) {
 }
 // the closures of yocto_sceneio.cpp:3690-3726 as a typed switch; q is local
 VPT_FN float eval_sdf_fn(const sdf_fn& s, f3 q) {
+  VPT_WORK(sdf_fn_evals, 1);
   switch (s.type) {
     case sdf_bbox: return sd_bbox(q, f3{s.params.y, s.params.z, s.params.w}, s.params.x);
     case sdf_box: return sd_box(q - (s.whd * 0.5f), s.whd * 0.5f);
@@ -77,6 +78,7 @@ VPT_FN vol_inst ld_vol_instance(const DScene& sc, int id) {
 
 // eval_volume (yocto_sdfs.cpp:92-127): clamped trilinear, 8 scalar loads
 VPT_FN float eval_volume(const DScene& sc, int w, int h, int d, int offset, f3 uvw) {
+  VPT_WORK(trilinear, 1);
   if (w * h * d == 0) return 0;
   auto s = vclamp((uvw.x + 1.0f) * 0.5f, 0.0f, 1.0f) * (w - 1);
   auto t = vclamp((uvw.y + 1.0f) * 0.5f, 0.0f, 1.0f) * (h - 1);
@@ -95,6 +97,7 @@ VPT_FN float eval_volume(const DScene& sc, int w, int h, int d, int offset, f3 u
 
 // eval_sdf(volume, instance, p, t) (yocto_sdfs.cpp:30-49); p is already local
 VPT_FN float eval_sdf_grid(const DScene& sc, const vol_inst& in, f3 p, float t) {
+  VPT_WORK(sdf_grid_evals, 1);
   auto v0 = ld4(sc.volumes + 2 * in.volume), v1 = ld4(sc.volumes + 2 * in.volume + 1);
   int  w = f2i(v0.x), h = f2i(v0.y), d = f2i(v0.z);
   auto res       = v0.w;
@@ -118,6 +121,7 @@ struct sdf_result {
 // eval_sdf_scene (yocto_sdfs.cpp:7-26): linear scan, grids first
 VPT_FN sdf_result eval_sdf_scene(const DScene& sc, f3 p, float t) {
   auto res = sdf_result{flt_max, invalidid, invalidid};
+  VPT_WORK(sdf_scene_evals, 1);
   for (auto idx = 0; idx < sc.num_vol_instances; idx++) {
     auto in = ld_vol_instance(sc, idx);
     auto v  = eval_sdf_grid(sc, in, transform_point(in.frame, p), t);

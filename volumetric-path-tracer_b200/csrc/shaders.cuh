@@ -341,6 +341,7 @@ VPT_FN f4 shade_path(const DScene& sc, const DParams& prm, const ray3& ray, rng_
   VPT_GUARD_DECL(guard);
   while (alive) {
     VPT_GUARD_STEP(3, guard, 1000);
+    VPT_WORK(bounces, 1);
     auto      isec = find_hit<S>(sc, prm, p, st);
     pending_t pd;
     auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);

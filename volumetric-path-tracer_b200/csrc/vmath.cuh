@@ -44,6 +44,23 @@ __device__ int vpt_guard_flags[16];
 #define VPT_COUNT_MAX(id, v)
 #endif
 
+// Work counters, compiled only into tests/hostsim (VPT_WORK_COUNTERS): they
+// measure the algorithmic work per path that the roofline in bench.py uses.
+#if defined(VPT_WORK_COUNTERS) && !defined(__CUDACC__)
+#include <atomic>
+namespace vpt {
+struct work_counters {
+  std::atomic<long long> box_tests{0}, tri_tests{0}, inst_transforms{0}, scene_queries{0},
+      instance_queries{0}, sdf_scene_evals{0}, sdf_fn_evals{0}, sdf_grid_evals{0},
+      trilinear{0}, bounces{0}, lightpdf_calls{0}, texel_reads{0};
+};
+inline work_counters g_work;
+}  // namespace vpt
+#define VPT_WORK(field, n) (vpt::g_work.field += (n))
+#else
+#define VPT_WORK(field, n)
+#endif
+
 namespace vpt {
 
 constexpr float pif     = 3.14159265358979323846f;
@@ -91,25 +108,139 @@ VPT_FN float vsin(float a) { return (float)sin((double)a); }
 VPT_FN float vcos(float a) { return (float)cos((double)a); }
 VPT_FN float vlog(float a) { return (float)log((double)a); }
 VPT_FN float vexp(float a) { return (float)exp((double)a); }
-VPT_FN float vatan(float a) { return (float)atan((double)a); }
 VPT_FN float vpow(float a, float b) { return (float)pow((double)a, (double)b); }
 #else
 VPT_FN float vsin(float a) { return sinf(a); }
 VPT_FN float vcos(float a) { return cosf(a); }
 VPT_FN float vlog(float a) { return logf(a); }
 VPT_FN float vexp(float a) { return expf(a); }
-VPT_FN float vatan(float a) { return atanf(a); }
 VPT_FN float vpow(float a, float b) { return powf(a, b); }
 #endif
-// Environment lookups happen once per path; evaluating them in double keeps
-// the deterministic shaders' miss pixels on the reference's bits.
-#if defined(__CUDA_ARCH__)
-VPT_FN float vatan2(float a, float b) { return (float)atan2((double)a, (double)b); }
-VPT_FN float vacos(float a) { return (float)acos((double)a); }
-#else
-VPT_FN float vatan2(float a, float b) { return atan2f(a, b); }
-VPT_FN float vacos(float a) { return acosf(a); }
-#endif
+// atanf / atan2f / acosf: the reference links glibc 2.39, whose float versions
+// are the fdlibm float algorithms (sysdeps/ieee754/flt-32/s_atanf.c, e_atan2f.c,
+// e_acosf.c; not correctly rounded). They use only + - * / sqrt on floats, so
+// restating them here keeps environment lookups (atan2, acos) and GGX sampling
+// (atan) on the reference's exact bits, on the device and in tests/hostsim.
+VPT_FN float vatan(float x) {
+  const float atanhi[4] = {4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f,
+      1.5707962513e+00f};
+  const float atanlo[4] = {5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f,
+      7.5497894159e-08f};
+  const float aT[11] = {3.3333334327e-01f, -2.0000000298e-01f, 1.4285714924e-01f,
+      -1.1111110449e-01f, 9.0908870101e-02f, -7.6918758452e-02f, 6.6610731184e-02f,
+      -5.8335702866e-02f, 4.9768779427e-02f, -3.6531571299e-02f, 1.6285819933e-02f};
+  int hx = f2i(x), ix = hx & 0x7fffffff, id;
+  if (ix >= 0x4c000000) {  // |x| >= 2^25 (glibc 2.39 threshold)
+    if (ix > 0x7f800000) return x + x;
+    return hx > 0 ? atanhi[3] + atanlo[3] : -atanhi[3] - atanlo[3];
+  }
+  if (ix < 0x3ee00000) {  // |x| < 0.4375
+    if (ix < 0x31000000) return x;  // |x| < 2^-29
+    id = -1;
+  } else {
+    x = vabs(x);
+    if (ix < 0x3f980000) {  // |x| < 1.1875
+      if (ix < 0x3f300000) {
+        id = 0;
+        x  = (2.0f * x - 1.0f) / (2.0f + x);
+      } else {
+        id = 1;
+        x  = (x - 1.0f) / (x + 1.0f);
+      }
+    } else {
+      if (ix < 0x401c0000) {  // |x| < 2.4375
+        id = 2;
+        x  = (x - 1.5f) / (1.0f + 1.5f * x);
+      } else {
+        id = 3;
+        x  = -1.0f / x;
+      }
+    }
+  }
+  float z  = x * x;
+  float w  = z * z;
+  float s1 = z * (aT[0] + w * (aT[2] + w * (aT[4] + w * (aT[6] + w * (aT[8] + w * aT[10])))));
+  float s2 = w * (aT[1] + w * (aT[3] + w * (aT[5] + w * (aT[7] + w * aT[9]))));
+  if (id < 0) return x - x * (s1 + s2);
+  float hi = id == 0 ? atanhi[0] : (id == 1 ? atanhi[1] : (id == 2 ? atanhi[2] : atanhi[3]));
+  float lo = id == 0 ? atanlo[0] : (id == 1 ? atanlo[1] : (id == 2 ? atanlo[2] : atanlo[3]));
+  z        = hi - ((x * (s1 + s2) - lo) - x);
+  return (hx < 0) ? -z : z;
+}
+VPT_FN float vatan2(float y, float x) {
+  const float tiny = 1.0e-30f, pi_o_4 = 7.8539818525e-01f, pi_o_2 = 1.5707963705e+00f,
+              pi = 3.1415927410e+00f, pi_lo = -8.7422776573e-08f;
+  int hx = f2i(x), ix = hx & 0x7fffffff, hy = f2i(y), iy = hy & 0x7fffffff;
+  if (ix > 0x7f800000 || iy > 0x7f800000) return x + y;
+  if (hx == 0x3f800000) return vatan(y);
+  int m = ((hy >> 31) & 1) | ((hx >> 30) & 2);
+  if (iy == 0) {
+    if (m < 2) return y;
+    return m == 2 ? pi + tiny : -pi - tiny;
+  }
+  if (ix == 0) return (hy < 0) ? -pi_o_2 - tiny : pi_o_2 + tiny;
+  if (ix == 0x7f800000) {
+    if (iy == 0x7f800000) {
+      if (m == 0) return pi_o_4 + tiny;
+      if (m == 1) return -pi_o_4 - tiny;
+      if (m == 2) return 3.0f * pi_o_4 + tiny;
+      return -3.0f * pi_o_4 - tiny;
+    }
+    if (m == 0) return 0.0f;
+    if (m == 1) return -0.0f;
+    if (m == 2) return pi + tiny;
+    return -pi - tiny;
+  }
+  if (iy == 0x7f800000) return (hy < 0) ? -pi_o_2 - tiny : pi_o_2 + tiny;
+  int   k = (iy - ix) >> 23;
+  float z;
+  if (k > 60)
+    z = pi_o_2 + 0.5f * pi_lo;
+  else if (hx < 0 && k < -60)
+    z = 0.0f;
+  else
+    z = vatan(vabs(y / x));
+  if (m == 0) return z;
+  if (m == 1) return i2f(f2i(z) ^ (int)0x80000000);
+  if (m == 2) return pi - (z - pi_lo);
+  return (z - pi_lo) - pi;
+}
+VPT_FN float vacos(float x) {
+  const float pi = 3.1415925026e+00f, pio2_hi = 1.5707962513e+00f, pio2_lo = 7.5497894159e-08f,
+              pS0 = 1.6666667163e-01f, pS1 = -3.2556581497e-01f, pS2 = 2.0121252537e-01f,
+              pS3 = -4.0055535734e-02f, pS4 = 7.9153501429e-04f, pS5 = 3.4793309169e-05f,
+              qS1 = -2.4033949375e+00f, qS2 = 2.0209457874e+00f, qS3 = -6.8828397989e-01f,
+              qS4 = 7.7038154006e-02f;
+  int hx = f2i(x), ix = hx & 0x7fffffff;
+  if (ix == 0x3f800000) return hx > 0 ? 0.0f : pi + 2.0f * pio2_lo;
+  if (ix > 0x3f800000) return (x - x) / (x - x);
+  if (ix < 0x3f000000) {  // |x| < 0.5
+    if (ix <= 0x23000000) return pio2_hi + pio2_lo;
+    float z = x * x;
+    float p = z * (pS0 + z * (pS1 + z * (pS2 + z * (pS3 + z * (pS4 + z * pS5)))));
+    float q = 1.0f + z * (qS1 + z * (qS2 + z * (qS3 + z * qS4)));
+    float r = p / q;
+    return pio2_hi - (x - (pio2_lo - x * r));
+  } else if (hx < 0) {  // x < -0.5
+    float z = (1.0f + x) * 0.5f;
+    float p = z * (pS0 + z * (pS1 + z * (pS2 + z * (pS3 + z * (pS4 + z * pS5)))));
+    float q = 1.0f + z * (qS1 + z * (qS2 + z * (qS3 + z * qS4)));
+    float s = vsqrt(z);
+    float r = p / q;
+    float w = r * s - pio2_lo;
+    return pi - 2.0f * (s + w);
+  } else {  // x > 0.5
+    float z  = (1.0f - x) * 0.5f;
+    float s  = vsqrt(z);
+    float df = i2f(f2i(s) & (int)0xfffff000);
+    float c  = (z - df * df) / (s + df);
+    float p  = z * (pS0 + z * (pS1 + z * (pS2 + z * (pS3 + z * (pS4 + z * pS5)))));
+    float q  = 1.0f + z * (qS1 + z * (qS2 + z * (qS3 + z * qS4)));
+    float r  = p / q;
+    float w  = r * s + c;
+    return 2.0f * (df + w);
+  }
+}
 VPT_FN float vfmod(float a, float b) { return fmodf(a, b); }
 
 // ---- f2 --------------------------------------------------------------------

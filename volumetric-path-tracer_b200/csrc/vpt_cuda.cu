@@ -227,6 +227,19 @@ int vpt_cuda_set_device(int device) {
 
 const char* vpt_cuda_last_error(void) { return g_last_error.c_str(); }
 
+int vpt_cuda_host_register(void* ptr, size_t bytes) {
+  if (!ptr || !bytes) return set_error(VPT_ERR_INVALID, "null argument");
+  if (auto r = require_device()) return r;
+  VPT_CUDA_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+  return VPT_OK;
+}
+
+int vpt_cuda_host_unregister(void* ptr) {
+  if (!ptr) return set_error(VPT_ERR_INVALID, "null argument");
+  VPT_CUDA_TRY(cudaHostUnregister(ptr));
+  return VPT_OK;
+}
+
 int vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out) {
   if (!desc || !out) return set_error(VPT_ERR_INVALID, "null argument");
   *out = nullptr;
@@ -334,8 +347,11 @@ int vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params*
 
   bool path_shader = prm.shader == shader_volpathtrace || prm.shader == shader_pathtrace ||
                      prm.shader == shader_naive || prm.shader == shader_implicit;
+  // auto: the mesh path shaders run as a wavefront; sphere tracing is pure ALU with no
+  // traversal stage to split off and measures faster in the megakernel
   bool wavefront = params->pipeline == VPT_PIPELINE_WAVEFRONT ||
-                   (params->pipeline == VPT_PIPELINE_AUTO && path_shader && false);
+                   (params->pipeline == VPT_PIPELINE_AUTO && path_shader &&
+                       prm.shader != shader_implicit);
 
   VPT_CUDA_TRY(cudaEventRecord(state->ev0));
   int launches = 0;

@@ -1,16 +1,345 @@
-// wavefront.cuh — placeholder until the wavefront pipeline lands (next commit).
+// wavefront.cuh — the path loop as a wavefront pipeline.
+//
+// One path slot per pixel (slot order = 8x4 pixel tiles). A slot owns its
+// pixel's PCG32 stream and runs that pixel's samples one after the other, so
+// the random streams replay exactly as in the reference / the megakernel and
+// both pipelines produce bit-identical images. Per bounce ("iteration"):
+//
+//   k_wf_extend    closest hit (BVH) or sphere-trace for every queued slot
+//   k_wf_shade     shade_hit: emission, opacity, BSDF / phase / light sampling;
+//                  paths that need the MIS light pdf go to the pdf queue, the
+//                  rest run bounce_tail and go to the next extend queue
+//   k_wf_lightpdf  sample_lights_pdf (instance-targeted traversals, sdf march,
+//                  environment texel pdf), weight update, bounce_tail
+//
+// A path that ends is accumulated into the image by its owner thread and the
+// slot regenerates the pixel's next camera sample in place (path regeneration),
+// so many samples run per launch without a host round trip. Queues hold slot
+// ids and are compacted with warp-aggregated appends: __ballot_sync + __popc
+// give each lane its rank, one atomicAdd per warp reserves the range.
+// Per-slot state is SoA of 16-byte records (coalesced 128-bit loads / stores).
 #pragma once
+
 #include <cuda_runtime.h>
+
 #include "../../include/vpt_cuda.h"
 #include "shaders.cuh"
+#include "tiling.cuh"
 #include "upload.cuh"
+
 namespace vpt {
-struct wavefront_buffers {
-  bool live = false;
-  void release() {}
+
+constexpr int wf_block = 128;
+
+struct wf_counters {
+  int                count_ext[2];  // extend queue sizes (double buffered)
+  int                count_pdf;
+  int                pad;
+  unsigned long long rays_extend, rays_lightpdf, paths_done;
 };
-inline cudaError_t run_wavefront(const flat_scene&, wavefront_buffers&, const DParams&, f4*,
-    rng_t*, int, int*, vpt_trace_stats*) {
-  return cudaErrorNotSupported;
+
+// device pointers of one state's wavefront buffers
+struct wf_view {
+  f4 *        a0, *a1, *a2, *a3, *a4, *a5, *v0, *v1, *v2;
+  int *       queue_ext[2], *queue_pdf;
+  wf_counters* counters;
+};
+
+struct wavefront_buffers {
+  bool         live     = false;
+  int          capacity = 0;
+  wf_view      view{};
+  wf_counters* host_counters = nullptr;  // pinned
+  cudaEvent_t  poll = nullptr, k0 = nullptr, k1 = nullptr;
+  void release() {
+    if (!capacity) return;
+    cudaFree(view.a0);
+    cudaFree(view.queue_ext[0]);
+    cudaFree(view.counters);
+    if (host_counters) cudaFreeHost(host_counters);
+    if (poll) cudaEventDestroy(poll);
+    if (k0) cudaEventDestroy(k0);
+    if (k1) cudaEventDestroy(k1);
+    *this = wavefront_buffers{};
+  }
+  cudaError_t reserve(int slots) {
+    if (capacity >= slots) return cudaSuccess;
+    release();
+    f4*  block = nullptr;
+    auto e     = cudaMalloc(&block, sizeof(f4) * 9 * (size_t)slots);
+    if (e != cudaSuccess) return e;
+    f4** arrays[9] = {&view.a0, &view.a1, &view.a2, &view.a3, &view.a4, &view.a5, &view.v0,
+        &view.v1, &view.v2};
+    for (int i = 0; i < 9; i++) *arrays[i] = block + (size_t)i * slots;
+    int* q = nullptr;
+    e      = cudaMalloc(&q, sizeof(int) * 3 * (size_t)slots);
+    if (e != cudaSuccess) return e;
+    view.queue_ext[0] = q, view.queue_ext[1] = q + slots, view.queue_pdf = q + 2 * (size_t)slots;
+    e = cudaMalloc(&view.counters, sizeof(wf_counters));
+    if (e == cudaSuccess) e = cudaMallocHost(&host_counters, sizeof(wf_counters));
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&poll, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreate(&k0);
+    if (e == cudaSuccess) e = cudaEventCreate(&k1);
+    if (e != cudaSuccess) return e;
+    capacity = slots;
+    return cudaSuccess;
+  }
+};
+
+#if defined(__CUDACC__)
+
+// ---- per-slot state <-> registers -------------------------------------------
+constexpr int wf_bit_hit = 1 << 16, wf_bit_vol = 1 << 17, wf_bit_isec = 1 << 18;
+
+template <int S>
+__device__ __forceinline__ void wf_store_path(const wf_view& w, int slot, const path_t& p,
+    int remaining) {
+  int flags = (p.bounce & 0xffff) | (p.hit ? wf_bit_hit : 0) | (p.in_volume ? wf_bit_vol : 0);
+  w.a0[slot] = {p.o.x, p.o.y, p.o.z, p.d.x};
+  w.a1[slot] = {p.d.y, p.d.z, i2f(flags), i2f(remaining)};
+  w.a2[slot] = {p.radiance.x, p.radiance.y, p.radiance.z, p.weight.x};
+  w.a3[slot] = {p.weight.y, p.weight.z, p.vol_anisotropy, 0};
+  if (S == shader_volpathtrace) {
+    w.v0[slot] = {p.vol_density.x, p.vol_density.y, p.vol_density.z, p.vol_scattering.x};
+    w.v1[slot] = {p.vol_scattering.y, p.vol_scattering.z, p.vol_emission.x, p.vol_emission.y};
+    w.v2[slot] = {p.vol_emission.z, 0, 0, 0};
+  }
 }
+
+template <int S>
+__device__ __forceinline__ void wf_load_path(const wf_view& w, int slot, path_t& p,
+    int& remaining) {
+  auto a0 = w.a0[slot], a1 = w.a1[slot], a2 = w.a2[slot], a3 = w.a3[slot];
+  p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
+  int flags = f2i(a1.z);
+  remaining = f2i(a1.w);
+  p.bounce = flags & 0xffff, p.hit = (flags & wf_bit_hit) != 0;
+  p.in_volume = (flags & wf_bit_vol) != 0;
+  p.radiance = {a2.x, a2.y, a2.z}, p.weight = {a2.w, a3.x, a3.y};
+  p.vol_anisotropy = a3.z;
+  if (S == shader_volpathtrace) {
+    auto v0 = w.v0[slot], v1 = w.v1[slot], v2 = w.v2[slot];
+    p.vol_density = {v0.x, v0.y, v0.z}, p.vol_scattering = {v0.w, v1.x, v1.y};
+    p.vol_emission = {v1.z, v1.w, v2.x};
+  } else {
+    p.vol_density = p.vol_scattering = p.vol_emission = {0, 0, 0};
+  }
+}
+
+// warp-aggregated append of `slot` to a queue for the lanes with `push` set
+__device__ __forceinline__ void wf_push(int* queue, int* count, bool push, int slot) {
+  unsigned mask = __ballot_sync(0xffffffffu, push);
+  if (!mask) return;
+  int lane   = threadIdx.x & 31;
+  int leader = __ffs(mask) - 1;
+  int base   = 0;
+  if (lane == leader) base = atomicAdd(count, __popc(mask));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (push) queue[base + __popc(mask & ((1u << lane) - 1))] = slot;
+}
+
+// A finished path: accumulate (owner thread, no atomics), then regenerate the
+// pixel's next camera sample in place. Returns false when the slot is done.
+template <int S>
+__device__ __forceinline__ bool wf_finish(const DScene& sc, const DParams& prm, int idx,
+    path_t& p, rng_t& rng, f4* image, int& remaining) {
+  auto rad   = guard_radiance(path_result(S, p));
+  image[idx] = image[idx] + rad;
+  remaining -= 1;
+  if (remaining <= 0) return false;
+  auto ray = sample_camera(sc, prm, idx, rng);
+  path_init(p, ray);
+  return true;
+}
+
+// ---- kernels -----------------------------------------------------------------
+template <int S>
+__global__ void __launch_bounds__(wf_block)
+    k_wf_init(const DScene sc, const DParams prm, wf_view w, rng_t* __restrict__ rngs, int slots,
+        int nsamples) {
+  int  slot   = blockIdx.x * blockDim.x + threadIdx.x;
+  bool active = false;
+  if (slot < slots) {
+    int idx = tile_pixel_index(slot, prm.width, prm.height);
+    if (idx >= 0) {
+      auto   rng = rngs[idx];
+      path_t p;
+      path_init(p, sample_camera(sc, prm, idx, rng));
+      wf_store_path<S>(w, slot, p, nsamples);
+      rngs[idx] = rng;
+      active    = true;
+    }
+  }
+  wf_push(w.queue_ext[0], &w.counters->count_ext[0], active, slot);
+}
+
+template <int S>
+__global__ void __launch_bounds__(wf_block)
+    k_wf_extend(const DScene sc, const DParams prm, wf_view w, int cur) {
+  extern __shared__ int stack_mem[];
+  int  tid   = blockIdx.x * blockDim.x + threadIdx.x;
+  int  count = w.counters->count_ext[cur];
+  if (tid == 0) {
+    // the queues written later in this iteration start empty
+    w.counters->count_ext[cur ^ 1] = 0;
+    w.counters->count_pdf          = 0;
+    w.counters->rays_extend += (unsigned long long)count;
+  }
+  if (tid >= count) return;
+  int     slot = w.queue_ext[cur][tid];
+  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  auto    a0 = w.a0[slot], a1 = w.a1[slot];
+  path_t  p;
+  p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
+  auto isec  = find_hit<S>(sc, prm, p, st);
+  w.a4[slot] = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
+  w.a3[slot].w = isec.distance;
+  w.a1[slot].z = i2f((f2i(a1.z) & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
+}
+
+template <int S>
+__global__ void __launch_bounds__(wf_block)
+    k_wf_shade(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
+        rng_t* __restrict__ rngs, int cur) {
+  int  tid      = blockIdx.x * blockDim.x + threadIdx.x;
+  int  count    = w.counters->count_ext[cur];
+  bool to_ext   = false, to_pdf = false;
+  int  slot     = 0;
+  if (tid < count) {
+    slot    = w.queue_ext[cur][tid];
+    int idx = tile_pixel_index(slot, prm.width, prm.height);
+    path_t p;
+    int    remaining;
+    wf_load_path<S>(w, slot, p, remaining);
+    auto a4   = w.a4[slot];
+    auto isec = isect_t{(f2i(w.a1[slot].z) & wf_bit_isec) != 0, f2i(a4.x), f2i(a4.y),
+        {a4.z, a4.w}, w.a3[slot].w};
+    auto      rng = rngs[idx];
+    pending_t pd;
+    auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);
+    if (r == step_lightpdf) {
+      w.a5[slot] = {pd.f.x, pd.f.y, pd.f.z, pd.bpdf};
+      to_pdf     = true;
+    } else {
+      bool alive = r == step_skip;
+      if (r == step_continue) alive = bounce_tail<S>(prm, p, rng);
+      if (!alive) alive = wf_finish<S>(sc, prm, idx, p, rng, image, remaining);
+      to_ext = alive;
+    }
+    wf_store_path<S>(w, slot, p, remaining);
+    rngs[idx] = rng;
+  }
+  wf_push(w.queue_ext[cur ^ 1], &w.counters->count_ext[cur ^ 1], to_ext, slot);
+  wf_push(w.queue_pdf, &w.counters->count_pdf, to_pdf, slot);
+}
+
+template <int S>
+__global__ void __launch_bounds__(wf_block)
+    k_wf_lightpdf(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
+        rng_t* __restrict__ rngs, int cur) {
+  extern __shared__ int stack_mem[];
+  int  tid    = blockIdx.x * blockDim.x + threadIdx.x;
+  int  count  = w.counters->count_pdf;
+  bool to_ext = false;
+  int  slot   = 0;
+  if (tid == 0) w.counters->rays_lightpdf += (unsigned long long)count;
+  if (tid < count) {
+    slot    = w.queue_pdf[tid];
+    int idx = tile_pixel_index(slot, prm.width, prm.height);
+    stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+    path_t  p;
+    int     remaining;
+    wf_load_path<S>(w, slot, p, remaining);
+    auto a5 = w.a5[slot];
+    auto pd = pending_t{p.o, p.d, {a5.x, a5.y, a5.z}, a5.w};
+    // after shade_hit the next ray is (position, incoming): the pdf is taken along it
+    auto lpdf = sample_lights_pdf(sc, p.o, p.d, prm.spheretrace_maxiter, st);
+    apply_lightpdf(p, pd, lpdf);
+    auto rng   = rngs[idx];
+    bool alive = bounce_tail<S>(prm, p, rng);
+    if (!alive) alive = wf_finish<S>(sc, prm, idx, p, rng, image, remaining);
+    to_ext = alive;
+    wf_store_path<S>(w, slot, p, remaining);
+    rngs[idx] = rng;
+  }
+  wf_push(w.queue_ext[cur ^ 1], &w.counters->count_ext[cur ^ 1], to_ext, slot);
+}
+
+// ---- host driver ---------------------------------------------------------------
+template <int S>
+cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
+    const DParams& prm, f4* image, rng_t* rngs, int nsamples, int* launches,
+    vpt_trace_stats* stats) {
+  int  slots = tile_slot_count(prm.width, prm.height);
+  auto e     = wf.reserve(slots);
+  if (e != cudaSuccess) return e;
+  auto&  w    = wf.view;
+  size_t smem = (size_t)scene.stack_depth * wf_block * sizeof(int);
+  if (smem > 48 * 1024) {
+    e = cudaFuncSetAttribute(k_wf_extend<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(k_wf_lightpdf<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+          (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  e = cudaMemsetAsync(w.counters, 0, sizeof(wf_counters));
+  if (e != cudaSuccess) return e;
+  int grid_all = (slots + wf_block - 1) / wf_block;
+  k_wf_init<S><<<grid_all, wf_block>>>(scene.d, prm, w, rngs, slots, nsamples);
+  *launches    = 1;
+  int   active = slots, cur = 0;
+  float extend_ms = 0;
+  bool  timed     = false;
+  while (active > 0) {
+    int grid = (active + wf_block - 1) / wf_block;
+    for (int it = 0; it < 8; it++) {
+      if (!timed) cudaEventRecord(wf.k0);
+      k_wf_extend<S><<<grid, wf_block, smem>>>(scene.d, prm, w, cur);
+      if (!timed) cudaEventRecord(wf.k1);
+      k_wf_shade<S><<<grid, wf_block>>>(scene.d, prm, w, image, rngs, cur);
+      k_wf_lightpdf<S><<<grid, wf_block, smem>>>(scene.d, prm, w, image, rngs, cur);
+      cur ^= 1;
+      *launches += 3;
+      if (!timed) {
+        // the first (full-occupancy) extend launch is the per-kernel sample the
+        // bench reports next to the whole-call time
+        timed = true;
+      }
+    }
+    e = cudaMemcpyAsync(wf.host_counters, w.counters, sizeof(wf_counters), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return e;
+    e = cudaEventRecord(wf.poll);
+    if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
+    if (e != cudaSuccess) return e;
+    active = wf.host_counters->count_ext[cur];
+  }
+  if (cudaEventElapsedTime(&extend_ms, wf.k0, wf.k1) == cudaSuccess)
+    stats->top_kernel_ms = extend_ms;
+  stats->rays_extend   = wf.host_counters->rays_extend;
+  stats->rays_lightpdf = wf.host_counters->rays_lightpdf;
+  return cudaGetLastError();
+}
+
+inline cudaError_t run_wavefront(const flat_scene& scene, wavefront_buffers& wf,
+    const DParams& prm, f4* image, rng_t* rngs, int nsamples, int* launches,
+    vpt_trace_stats* stats) {
+  switch (prm.shader) {
+    case shader_volpathtrace:
+      return run_wavefront_shader<shader_volpathtrace>(scene, wf, prm, image, rngs, nsamples,
+          launches, stats);
+    case shader_pathtrace:
+      return run_wavefront_shader<shader_pathtrace>(scene, wf, prm, image, rngs, nsamples,
+          launches, stats);
+    case shader_naive:
+      return run_wavefront_shader<shader_naive>(scene, wf, prm, image, rngs, nsamples, launches,
+          stats);
+    case shader_implicit:
+      return run_wavefront_shader<shader_implicit>(scene, wf, prm, image, rngs, nsamples,
+          launches, stats);
+    default: return cudaErrorNotSupported;
+  }
+}
+
+#endif  // __CUDACC__
+
 }  // namespace vpt

@@ -20,6 +20,20 @@ struct vpth_render {
   pathtrace_params       params;
   pathtrace_state        state;
   std::vector<rng_state> initial_rngs;
+  std::vector<void*>     pinned;
+  // page-lock the host mirrors once a device exists (best effort)
+  void pin() {
+    if (!pinned.empty() || vpt_cuda_device_count() < 1) return;
+    auto reg = [&](void* p, size_t n) {
+      if (n && vpt_cuda_host_register(p, n) == VPT_OK) pinned.push_back(p);
+    };
+    reg(initial_rngs.data(), initial_rngs.size() * sizeof(rng_state));
+    reg(state.rngs.data(), state.rngs.size() * sizeof(rng_state));
+    reg(state.image.data(), state.image.size() * sizeof(vec4f));
+  }
+  ~vpth_render() {
+    for (auto p : pinned) vpt_cuda_host_unregister(p);
+  }
 };
 
 static thread_local std::string g_error;
@@ -205,6 +219,7 @@ int vpth_render_samples(vpth_render* r, int nsamples) {
     auto s = r->owner;
     if (!s->device) s->device = upload_scene(s->scene, s->bvh, s->lights);
     bind_device_scene(r->state, s->device, s->scene, s->bvh, s->lights);
+    r->pin();
     auto params  = r->params;
     params.batch = nsamples;
     pathtrace_samples(r->state, s->scene, s->bvh, s->lights, params);
