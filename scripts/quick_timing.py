@@ -1,4 +1,5 @@
-import sys, time
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as e
 p = e.load_package(); b = p.binding
 b.set_device(0)

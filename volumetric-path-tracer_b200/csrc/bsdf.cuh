@@ -424,7 +424,7 @@ VPT_FN f3 eval_emission(const material_point& m, f3 normal, f3 outgoing) {
   return dot(normal, outgoing) >= 0 ? m.emission : f3{0, 0, 0};
 }
 
-VPT_FN f3 eval_bsdfcos(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
+VPT_CALL f3 eval_bsdfcos(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
   if (m.roughness == 0) return {0, 0, 0};
   switch (m.type) {
     case mat_matte: return eval_matte(m.color, normal, outgoing, incoming);
@@ -439,7 +439,7 @@ VPT_FN f3 eval_bsdfcos(const material_point& m, f3 normal, f3 outgoing, f3 incom
     default: return {0, 0, 0};
   }
 }
-VPT_FN f3 eval_delta(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
+VPT_CALL f3 eval_delta(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
   if (m.roughness != 0) return {0, 0, 0};
   switch (m.type) {
     case mat_reflective: return eval_reflective_delta(m.color, normal, outgoing, incoming);
@@ -449,7 +449,7 @@ VPT_FN f3 eval_delta(const material_point& m, f3 normal, f3 outgoing, f3 incomin
     default: return {0, 0, 0};
   }
 }
-VPT_FN f3 sample_bsdfcos(const material_point& m, f3 normal, f3 outgoing, float rnl, f2 rn) {
+VPT_CALL f3 sample_bsdfcos(const material_point& m, f3 normal, f3 outgoing, float rnl, f2 rn) {
   if (m.roughness == 0) return {0, 0, 0};
   switch (m.type) {
     case mat_matte: return sample_matte(normal, outgoing, rn);
@@ -463,7 +463,7 @@ VPT_FN f3 sample_bsdfcos(const material_point& m, f3 normal, f3 outgoing, float 
     default: return {0, 0, 0};
   }
 }
-VPT_FN f3 sample_delta(const material_point& m, f3 normal, f3 outgoing, float rnl) {
+VPT_CALL f3 sample_delta(const material_point& m, f3 normal, f3 outgoing, float rnl) {
   if (m.roughness != 0) return {0, 0, 0};
   switch (m.type) {
     case mat_reflective: return sample_reflective_delta(normal, outgoing);
@@ -473,7 +473,7 @@ VPT_FN f3 sample_delta(const material_point& m, f3 normal, f3 outgoing, float rn
     default: return {0, 0, 0};
   }
 }
-VPT_FN float sample_bsdfcos_pdf(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
+VPT_CALL float sample_bsdfcos_pdf(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
   if (m.roughness == 0) return 0;
   switch (m.type) {
     case mat_matte: return sample_matte_pdf(normal, outgoing, incoming);
@@ -490,7 +490,7 @@ VPT_FN float sample_bsdfcos_pdf(const material_point& m, f3 normal, f3 outgoing,
     default: return 0;
   }
 }
-VPT_FN float sample_delta_pdf(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
+VPT_CALL float sample_delta_pdf(const material_point& m, f3 normal, f3 outgoing, f3 incoming) {
   if (m.roughness != 0) return 0;
   switch (m.type) {
     case mat_reflective: return sample_reflective_delta_pdf(normal, outgoing, incoming);

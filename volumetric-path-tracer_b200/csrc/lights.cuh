@@ -39,7 +39,7 @@ VPT_FN float sample_discrete_pdf(const float* cdf, int idx) {
 VPT_FN int sample_uniform(int size, float r) { return vclamp((int)(r * size), 0, size - 1); }
 
 // sample_lights (yocto_pathtrace.cpp:312-350)
-VPT_FN f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2 ruv) {
+VPT_CALL f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2 ruv) {
   auto light_id = sample_uniform(sc.num_lights, rl);
   auto l0 = ld4(sc.lights + 2 * light_id), l1 = ld4(sc.lights + 2 * light_id + 1);
   if (l0.x != invalidid) {

@@ -80,7 +80,7 @@ VPT_FN f4 eval_texture_rec(const DScene& sc, i4 tex, f2 uv, bool as_linear) {
          lookup_texture(sc, tex, ii, jj, as_linear) * u * v;
 }
 
-VPT_FN f4 eval_texture(const DScene& sc, int texture, f2 uv, bool as_linear) {
+VPT_CALL f4 eval_texture(const DScene& sc, int texture, f2 uv, bool as_linear) {
   if (texture == invalidid) return {1, 1, 1, 1};
   return eval_texture_rec(sc, ld4(sc.textures + texture), uv, as_linear);
 }
@@ -270,7 +270,7 @@ VPT_FN void finish_material_point(material_point& point) {
 }
 
 // eval_material(scene, instance, element, uv) (yocto_scene.cpp:529-579)
-VPT_FN material_point eval_material(
+VPT_CALL material_point eval_material(
     const DScene& sc, const inst_ref& in, const material_t& m, int element, f2 uv) {
   auto texcoord       = eval_texcoord(sc, in, element, uv);
   auto emission_tex   = eval_texture(sc, m.emission_tex, texcoord, true);
@@ -369,7 +369,7 @@ VPT_FN f3 eval_normalmap(
   return normal;
 }
 
-VPT_FN f3 eval_shading_normal(const DScene& sc, const inst_ref& in, const material_t& m,
+VPT_CALL f3 eval_shading_normal(const DScene& sc, const inst_ref& in, const material_t& m,
     int element, f2 uv, f3 outgoing) {
   if (in.s.kind == kind_empty) return {0, 0, 0};
   auto normal = eval_normal(sc, in, element, uv);
@@ -385,7 +385,7 @@ VPT_FN f2 environment_texcoord(f3 wl) {
   return texcoord;
 }
 
-VPT_FN f3 eval_environment(const DScene& sc, f3 direction) {
+VPT_CALL f3 eval_environment(const DScene& sc, f3 direction) {
   auto emission = f3{0, 0, 0};
   for (auto e = 0; e < sc.num_environments; e++) {
     auto p   = sc.environments + 9 * e;

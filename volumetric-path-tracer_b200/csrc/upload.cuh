@@ -217,7 +217,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     inst_frame.push_back(pack(frame.z, 0));
     inst_frame.push_back(pack(frame.o, 0));
   }
-  int scene_root = -1, scene_depth = 0;
+  int scene_root = -1, scene_depth = 0, scene_leaf = 0;
   if (in.num_instances > 0) {
     auto& bvh = in.scene_bvh;
     if (bvh.num_nodes <= 0 || bvh.num_primitives != in.num_instances)
@@ -232,11 +232,17 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     }
     for (int n = 0; n < bvh.num_nodes; n++) {
       auto& node = bvh.nodes[n];
+      if (!node.internal) {
+        if (node.start < 0 || node.start + node.num > bvh.num_primitives)
+          return fail(VPT_ERR_INVALID, "scene bvh leaf out of range");
+        scene_leaf = node.num > scene_leaf ? node.num : scene_leaf;
+      }
       push_node(node, node.internal ? scene_root + node.start : node.start);
     }
   }
-  // DFS with the near child in a register keeps at most one entry per level
-  out.stack_depth = max_shape_depth + scene_depth + 2;
+  // one stack for both levels (bvh.cuh): a sibling per scene level, the queued
+  // instances of one scene leaf, the sentinel, then a sibling per shape level
+  out.stack_depth = scene_depth + 1 + scene_leaf + 1 + max_shape_depth + 1;
   if (out.stack_depth > vpt_stack_depth)
     return fail(VPT_ERR_UNSUPPORTED, "bvh deeper than the device traversal stack (" +
                                          std::to_string(out.stack_depth) + " > " +

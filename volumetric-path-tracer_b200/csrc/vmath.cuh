@@ -18,9 +18,19 @@
 #if defined(__CUDACC__)
 #define VPT_FN __host__ __device__ __forceinline__
 #define VPT_NOINLINE __host__ __device__ __noinline__
+// The big shared pieces of the shade stage (texture fetch, BSDF dispatch, light
+// sampling, environment) are real calls on the device: force-inlining them made
+// k_wf_shade 27k instructions (430 KB) and ncu showed it stalled on instruction
+// fetch (stall_no_instruction 14.7 warps per issue, issue slots 13% busy).
+#if defined(VPT_INLINE_ALL)
+#define VPT_CALL VPT_FN
+#else
+#define VPT_CALL __host__ __device__ __noinline__
+#endif
 #else
 #define VPT_FN inline
 #define VPT_NOINLINE inline
+#define VPT_CALL inline
 #endif
 
 // Debug-only loop guards (build with -DVPT_GUARD): a loop that exceeds its bound

@@ -18,8 +18,21 @@
 // ids and are compacted with warp-aggregated appends: __ballot_sync + __popc
 // give each lane its rank, one atomicAdd per warp reserves the range.
 // Per-slot state is SoA of 16-byte records (coalesced 128-bit loads / stores).
+//
+// Between extend and shade the queue is counting-sorted by shade class (miss,
+// inside-a-volume, surface material id): k_wf_extend takes a rank inside its
+// class (one atomicAdd per distinct class per warp, __match_any_sync),
+// k_wf_sort scatters the slot ids to class_base + rank. Warps of k_wf_shade
+// then run one material's code instead of all of them (ncu r01: 7.9 of 32
+// lanes and 15 warps stalled on instruction fetch per issue before sorting).
+// The order inside a class is arbitrary; pixels do not interact, so results
+// are unaffected.
 #pragma once
 
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
 #include <cuda_runtime.h>
 
 #include "../../include/vpt_cuda.h"
@@ -29,19 +42,22 @@
 
 namespace vpt {
 
-constexpr int wf_block = 128;
+constexpr int wf_block   = 128;
+constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped)
 
 struct wf_counters {
   int                count_ext[2];  // extend queue sizes (double buffered)
   int                count_pdf;
   int                pad;
   unsigned long long rays_extend, rays_lightpdf, paths_done;
+  int                class_count[wf_classes];
 };
 
 // device pointers of one state's wavefront buffers
 struct wf_view {
   f4 *        a0, *a1, *a2, *a3, *a4, *a5, *v0, *v1, *v2;
   int *       queue_ext[2], *queue_pdf;
+  int *       queue_shade, *sort_key;  // class-sorted slots; (class << 24 | rank) per entry
   wf_counters* counters;
 };
 
@@ -72,9 +88,10 @@ struct wavefront_buffers {
         &view.v1, &view.v2};
     for (int i = 0; i < 9; i++) *arrays[i] = block + (size_t)i * slots;
     int* q = nullptr;
-    e      = cudaMalloc(&q, sizeof(int) * 3 * (size_t)slots);
+    e      = cudaMalloc(&q, sizeof(int) * 5 * (size_t)slots);
     if (e != cudaSuccess) return e;
     view.queue_ext[0] = q, view.queue_ext[1] = q + slots, view.queue_pdf = q + 2 * (size_t)slots;
+    view.queue_shade = q + 3 * (size_t)slots, view.sort_key = q + 4 * (size_t)slots;
     e = cudaMalloc(&view.counters, sizeof(wf_counters));
     if (e == cudaSuccess) e = cudaMallocHost(&host_counters, sizeof(wf_counters));
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&poll, cudaEventDisableTiming);
@@ -195,6 +212,47 @@ __global__ void __launch_bounds__(wf_block)
   w.a4[slot] = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
   w.a3[slot].w = isec.distance;
   w.a1[slot].z = i2f((f2i(a1.z) & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
+  // shade class and the rank inside it
+  int cls = 0;
+  if (isec.hit) {
+    int material;
+    if (is_sdf_shader<S>())
+      material = isec.instance != invalidid ? f2i(ld4(sc.vol_instances + 4 * isec.instance + 2).w)
+                                            : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
+    else
+      material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);
+    cls = 2 + (material < wf_classes - 3 ? material : wf_classes - 3);
+    if (S == shader_volpathtrace && (f2i(a1.z) & wf_bit_vol)) cls = 1;
+  }
+  unsigned peers  = __match_any_sync(__activemask(), cls);
+  int      lane   = threadIdx.x & 31;
+  int      leader = __ffs(peers) - 1;
+  int      base   = 0;
+  if (lane == leader) base = atomicAdd(&w.counters->class_count[cls], __popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  w.sort_key[tid] = (cls << 24) | (base + __popc(peers & ((1u << lane) - 1)));
+}
+
+// scatter the extend queue into class order (counting sort, second pass)
+__global__ void __launch_bounds__(wf_block) k_wf_sort(wf_view w, int cur) {
+  __shared__ int base[wf_classes];
+  if (threadIdx.x < 32) {
+    // exclusive scan of the 64 class counts by one warp
+    int a = w.counters->class_count[2 * threadIdx.x], b = w.counters->class_count[2 * threadIdx.x + 1];
+    int sum = a + b, incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+      int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)threadIdx.x >= o) incl += v;
+    }
+    base[2 * threadIdx.x]     = incl - sum;
+    base[2 * threadIdx.x + 1] = incl - sum + a;
+  }
+  __syncthreads();
+  int tid   = blockIdx.x * blockDim.x + threadIdx.x;
+  int count = w.counters->count_ext[cur];
+  if (tid >= count) return;
+  int key = w.sort_key[tid];
+  w.queue_shade[base[key >> 24] + (key & 0xffffff)] = w.queue_ext[cur][tid];
 }
 
 template <int S>
@@ -205,8 +263,9 @@ __global__ void __launch_bounds__(wf_block)
   int  count    = w.counters->count_ext[cur];
   bool to_ext   = false, to_pdf = false;
   int  slot     = 0;
+  if (blockIdx.x == 0 && threadIdx.x < wf_classes) w.counters->class_count[threadIdx.x] = 0;
   if (tid < count) {
-    slot    = w.queue_ext[cur][tid];
+    slot    = w.queue_shade[tid];
     int idx = tile_pixel_index(slot, prm.width, prm.height);
     path_t p;
     int    remaining;
@@ -265,13 +324,108 @@ __global__ void __launch_bounds__(wf_block)
   wf_push(w.queue_ext[cur ^ 1], &w.counters->count_ext[cur ^ 1], to_ext, slot);
 }
 
+// Drain: below `wf_drain_threshold()` active slots an iteration no longer fills
+// the machine and its cost is the latency of three dependent launches, so the
+// remaining slots are finished by ONE launch in which each thread runs its slot
+// to the end (rest of the current path, then the pixel's remaining samples).
+// Same state machine, same order of arithmetic and RNG draws per pixel.
+template <int S>
+__global__ void __launch_bounds__(wf_block)
+    k_wf_drain(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
+        rng_t* __restrict__ rngs, int cur) {
+  extern __shared__ int stack_mem[];
+  int tid   = blockIdx.x * blockDim.x + threadIdx.x;
+  int count = w.counters->count_ext[cur];
+  unsigned long long n_ext = 0, n_pdf = 0;
+  if (tid < count) {
+    int     slot = w.queue_ext[cur][tid];
+    int     idx  = tile_pixel_index(slot, prm.width, prm.height);
+    stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+    path_t  p;
+    int     remaining;
+    wf_load_path<S>(w, slot, p, remaining);
+    auto rng   = rngs[idx];
+    auto alive = true;
+    while (alive) {  // single exit
+      auto      isec = find_hit<S>(sc, prm, p, st);
+      pending_t pd;
+      auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);
+      n_ext += 1;
+      if (r == step_lightpdf) {
+        auto lpdf = sample_lights_pdf(sc, pd.position, pd.incoming, prm.spheretrace_maxiter, st);
+        apply_lightpdf(p, pd, lpdf);
+        n_pdf += 1;
+      }
+      alive = r == step_skip;
+      if (r == step_continue || r == step_lightpdf) alive = bounce_tail<S>(prm, p, rng);
+      if (!alive) alive = wf_finish<S>(sc, prm, idx, p, rng, image, remaining);
+    }
+    rngs[idx] = rng;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    n_ext += __shfl_down_sync(0xffffffffu, n_ext, o);
+    n_pdf += __shfl_down_sync(0xffffffffu, n_pdf, o);
+  }
+  if ((threadIdx.x & 31) == 0 && n_ext) {
+    atomicAdd(&w.counters->rays_extend, n_ext);
+    atomicAdd(&w.counters->rays_lightpdf, n_pdf);
+  }
+}
+
+// active slots at or below which the wavefront hands over to k_wf_drain;
+// VPT_WF_DRAIN overrides (0 disables), for experiments and the parity tests
+inline int wf_drain_threshold(int slots) {
+  static const char* env = getenv("VPT_WF_DRAIN");
+  if (env) return atoi(env);
+  int t = slots / 8;
+  return t < 32768 ? t : 32768;
+}
+
+// VPT_WF_TRACE=<file>: per-iteration kernel times from CUDA events (a debugging
+// aid; the events perturb the run, so a traced call is not a bench value)
+struct wf_trace {
+  std::vector<cudaEvent_t> events;
+  std::vector<int>         grids;
+  const char*              path;
+  static std::unique_ptr<wf_trace> open() {
+    const char* env = getenv("VPT_WF_TRACE");
+    if (!env || !*env) return nullptr;
+    auto t  = std::make_unique<wf_trace>();
+    t->path = env;
+    return t;
+  }
+  void mark(int grid) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e);
+    events.push_back(e);
+    grids.push_back(grid);
+  }
+  void dump() {
+    cudaDeviceSynchronize();
+    if (auto f = fopen(path, "a")) {
+      fprintf(f, "iteration,grid,extend_us,shade_us,lightpdf_us\n");
+      for (size_t i = 0; i + 3 < events.size(); i += 4) {
+        float a = 0, b = 0, c = 0;
+        cudaEventElapsedTime(&a, events[i], events[i + 1]);
+        cudaEventElapsedTime(&b, events[i + 1], events[i + 2]);
+        cudaEventElapsedTime(&c, events[i + 2], events[i + 3]);
+        fprintf(f, "%zu,%d,%.1f,%.1f,%.1f\n", i / 4, grids[i], a * 1e3f, b * 1e3f, c * 1e3f);
+      }
+      fclose(f);
+    }
+    for (auto e : events) cudaEventDestroy(e);
+  }
+};
+
 // ---- host driver ---------------------------------------------------------------
 template <int S>
 cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     const DParams& prm, f4* image, rng_t* rngs, int nsamples, int* launches,
     vpt_trace_stats* stats) {
-  int  slots = tile_slot_count(prm.width, prm.height);
-  auto e     = wf.reserve(slots);
+  int slots = tile_slot_count(prm.width, prm.height);
+  if (slots >= (1 << 24)) return cudaErrorInvalidValue;  // sort_key packs the rank in 24 bits
+  auto e = wf.reserve(slots);
   if (e != cudaSuccess) return e;
   auto&  w    = wf.view;
   size_t smem = (size_t)scene.stack_depth * wf_block * sizeof(int);
@@ -290,16 +444,27 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   int   active = slots, cur = 0;
   float extend_ms = 0;
   bool  timed     = false;
+  int   drain_at  = wf_drain_threshold(slots);
+  auto  trace     = wf_trace::open();
+  if (smem > 48 * 1024) {
+    e = cudaFuncSetAttribute(k_wf_drain<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
   while (active > 0) {
     int grid = (active + wf_block - 1) / wf_block;
     for (int it = 0; it < 8; it++) {
       if (!timed) cudaEventRecord(wf.k0);
+      if (trace) trace->mark(grid);
       k_wf_extend<S><<<grid, wf_block, smem>>>(scene.d, prm, w, cur);
       if (!timed) cudaEventRecord(wf.k1);
+      k_wf_sort<<<grid, wf_block>>>(w, cur);
+      if (trace) trace->mark(grid);
       k_wf_shade<S><<<grid, wf_block>>>(scene.d, prm, w, image, rngs, cur);
+      if (trace) trace->mark(grid);
       k_wf_lightpdf<S><<<grid, wf_block, smem>>>(scene.d, prm, w, image, rngs, cur);
+      if (trace) trace->mark(grid);
       cur ^= 1;
-      *launches += 3;
+      *launches += 4;
       if (!timed) {
         // the first (full-occupancy) extend launch is the per-kernel sample the
         // bench reports next to the whole-call time
@@ -312,7 +477,18 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
     if (e != cudaSuccess) return e;
     active = wf.host_counters->count_ext[cur];
+    if (active > 0 && active <= drain_at) {
+      grid = (active + wf_block - 1) / wf_block;
+      k_wf_drain<S><<<grid, wf_block, smem>>>(scene.d, prm, w, image, rngs, cur);
+      *launches += 1;
+      e = cudaMemcpyAsync(wf.host_counters, w.counters, sizeof(wf_counters), cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess) e = cudaEventRecord(wf.poll);
+      if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
+      if (e != cudaSuccess) return e;
+      active = 0;
+    }
   }
+  if (trace) trace->dump();
   if (cudaEventElapsedTime(&extend_ms, wf.k0, wf.k1) == cudaSuccess)
     stats->top_kernel_ms = extend_ms;
   stats->rays_extend   = wf.host_counters->rays_extend;
