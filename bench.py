@@ -215,7 +215,7 @@ def gpu_arm(args, wl, rank, world, local_rank):
                            bounces=wl["bounces"], pipeline=args.pipeline)
     r = b.Render(scene, params)
     # sample-range sharding: rank r owns a disjoint stretch of every pixel's PCG32 stream
-    rng_offset = rank << 40
+    rng_offset = pkg.sharding.rank_rng_offset(rank)
     r.reset(rng_offset)
     paths_per_step = r.width * r.height * spp
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -260,7 +260,7 @@ def gpu_arm(args, wl, rank, world, local_rank):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+        pkg.sharding.reduce_images(acc, dst=0)
         e1.record()
         torch.cuda.synchronize()
         reduce_ms = e0.elapsed_time(e1)

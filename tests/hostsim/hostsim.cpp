@@ -15,6 +15,8 @@
 #define VPT_STACK_CHECK 1
 #define VPT_WORK_COUNTERS 1
 #include <chrono>
+#include <cmath>
+#include <cstring>
 #include <thread>
 
 #include "../../volumetric-path-tracer_b200/csrc/shaders.cuh"
@@ -51,7 +53,35 @@ static void render(const DScene& sc, const DParams& prm, pathtrace_state& state,
   for (auto& t : threads) t.join();
 }
 
+// `hostsim --selftest-math N`: the fdlibm restatements in vmath.cuh (what the device
+// runs for atan / atan2 / acos) against this box's libm float functions, bit for bit,
+// on N random arguments per function plus the edge cases. Prints the mismatch count.
+static int selftest_math(long n) {
+  auto bits = [](float x) { uint32_t u; memcpy(&u, &x, 4); return u; };
+  auto same = [&](float a, float b) { return bits(a) == bits(b) || (a != a && b != b); };
+  uint64_t s = 0x9e3779b97f4a7c15ull;
+  auto next = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16); };
+  auto anyf = [&]() { uint32_t u = next(); float f; memcpy(&f, &u, 4); return f; };
+  auto unit = [&]() { return ((int32_t)next()) / 2147483648.0f; };
+  long bad = 0;
+  float edges[] = {0.0f, -0.0f, 1.0f, -1.0f, 0.5f, -0.5f, 1e-30f, 1e30f, 3.4e38f, 0.4375f, 0.6875f,
+      1.1875f, 2.4375f, 33554432.0f, 33554431.0f, INFINITY, -INFINITY, NAN};
+  for (auto a : edges) {
+    bad += !same(vatan(a), atanf(a)) + !same(vacos(a), acosf(a));
+    for (auto b : edges) bad += !same(vatan2(a, b), atan2f(a, b));
+  }
+  for (long i = 0; i < n; i++) {
+    auto a = anyf(), b = anyf(), u = unit(), v = unit();
+    bad += !same(vatan(a), atanf(a)) + !same(vatan(u * 8), atanf(u * 8));
+    bad += !same(vatan2(a, b), atan2f(a, b)) + !same(vatan2(u, v), atan2f(u, v));
+    bad += !same(vacos(u), acosf(u)) + !same(vacos(a), acosf(a));
+  }
+  printf("math selftest: %ld mismatches in %ld x 6 + edges\n", bad, n);
+  return bad == 0 ? 0 : 1;
+}
+
 int main(int argc, const char** argv) {
+  if (argc == 3 && std::string(argv[1]) == "--selftest-math") return selftest_math(atol(argv[2]));
   if (argc < 3) {
     fprintf(stderr, "usage: hostsim scene.vptscene out.vptarch [opts]\n");
     return 2;

@@ -180,8 +180,9 @@ def test_progressive_and_sample_cap(vpt, scenes):
 
 def test_check_image_03_volume(vpt, scenes, root):
     """The reference's own golden: check/lowres/03_volume_720_256.jpg (sRGB JPEG q75), decoded
-    once into tests/golden/check_03_volume_720_256.npy. Tolerance: mean luminance within 2 %,
-    RMSE <= 0.03 on 3x3-blurred sRGB (JPEG noise + Monte-Carlo noise at 256 spp)."""
+    once into tests/golden/check_03_volume_720_256.npy. Tolerance: mean luminance within 1 %,
+    RMSE <= 0.02 on 3x3-blurred sRGB (the oracle itself scores 0.9998 / 0.0092: JPEG noise +
+    Monte-Carlo noise at 256 spp)."""
     import os
 
     gold = os.path.join(root, "tests", "golden", "check_03_volume_720_256.npy")
@@ -195,5 +196,5 @@ def test_check_image_03_volume(vpt, scenes, root):
     img = util.tonemap_srgb(r.image(normalized=True)[..., :3])
     r.close()
     assert img.shape == want.shape
-    assert abs(util.luminance(img).mean() / util.luminance(want).mean() - 1) <= 0.02
-    assert util.rmse(util.box_blur3(img), util.box_blur3(want)) <= 0.03
+    assert abs(util.luminance(img).mean() / util.luminance(want).mean() - 1) <= 0.01
+    assert util.rmse(util.box_blur3(img), util.box_blur3(want)) <= 0.02

@@ -5,4 +5,4 @@ importable name ``vpt_b200`` by ``__graft_entry__.load_package()``.
 Product code is C++/CUDA (csrc/, host/); the Python here is the ctypes binding
 and the fixture tooling used by tests/ and bench.py.
 """
-from . import archive, binding  # noqa: F401
+from . import archive, binding, sharding  # noqa: F401

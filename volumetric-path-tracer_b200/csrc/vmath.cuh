@@ -209,7 +209,7 @@ VPT_FN float vatan2(float y, float x) {
   else if (hx < 0 && k < -60)
     z = 0.0f;
   else
-    z = vatan(vabs(y / x));
+    z = vatan(i2f(f2i(y / x) & 0x7fffffff));  // fabsf: clears the sign of -0 too
   if (m == 0) return z;
   if (m == 1) return i2f(f2i(z) ^ (int)0x80000000);
   if (m == 2) return pi - (z - pi_lo);
