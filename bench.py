@@ -73,6 +73,28 @@ FLOPS = dict(box_tests=26, tri_tests=52, inst_transforms=30, bounces=300, sdf_sc
              sdf_fn_evals=45, sdf_grid_evals=43, trilinear=30)
 SM_COUNT, FP32_LANES = 148, 128
 
+# The dominant kernel is k_wf_extend (one closest-hit query per queued ray). Its algorithmic
+# work per RAY: the counters above minus the share spent in light-pdf instance queries
+# (hostsim iq_* counters), divided by the rays per path; bytes = nodes 32 B, primitives 48/64 B,
+# instance records 64 B, plus the ray read (32 B) and hit write (24 B) that must touch HBM.
+EXTEND = {
+    "03_volume": dict(box_tests=36.37, tri_tests=10.52, inst_transforms=6.06, prim_bytes=64),
+    "01_surface": dict(box_tests=22.45, tri_tests=4.02, inst_transforms=4.90, prim_bytes=48),
+}
+# dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend launch, from
+# profiles/r01_ncu_full_sorted_pipeline.brief.txt (ncu --set full), per launch like `achieved`
+NCU_TRAFFIC = {"03_volume": 32.8e6 + 12.4e6}
+
+
+def extend_flops_per_ray(name):
+    w = EXTEND.get(name)
+    return None if w is None else sum(w[k] * FLOPS[k] for k in ("box_tests", "tri_tests", "inst_transforms"))
+
+
+def extend_bytes_per_ray(name):
+    w = EXTEND[name]
+    return w["box_tests"] * 32 + w["tri_tests"] * w["prim_bytes"] + w["inst_transforms"] * 64 + 56
+
 
 def flops_per_path(name):
     return sum(WORK[name][k] * FLOPS[k] for k in FLOPS)
@@ -237,14 +259,17 @@ def gpu_arm(args, wl, rank, world, local_rank):
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    step_ms, launches, top_ms = [], 0, []
+    step_ms, launches = [], 0
+    top_ms, top_units, top_launches = 0.0, 0, 0
     for _ in range(args.steps):
         flush.zero_()
         torch.cuda.synchronize()
         r.trace(spp)
         st = r.stats()
         step_ms.append(st.device_ms)
-        top_ms.append(st.top_kernel_ms)
+        top_ms += st.top_kernel_ms
+        top_units += st.top_kernel_units
+        top_launches += st.top_kernel_launches
         launches += st.kernel_launches
     barrier()
     clocks = sampler.summary()
@@ -297,7 +322,22 @@ def gpu_arm(args, wl, rank, world, local_rank):
         fp32_peak = SM_COUNT * FP32_LANES * 2 * sm_max * 1e6 / 1e12
         fpp = flops_per_path(args.workload)
         ms_per_step = worst_ms / args.steps
-        achieved = fpp * paths_per_step / (ms_per_step / 1e3) / 1e12
+        step_tflops = fpp * paths_per_step / (ms_per_step / 1e3) / 1e12
+        wavefront = args.pipeline != "mega" and extend_flops_per_ray(args.workload) is not None \
+            and top_launches > 0 and wl["shader"] in ("volpathtrace", "pathtrace", "naive")
+        if wavefront:
+            # dominant kernel, timed live with CUDA events on its own stream (one launch per
+            # counter poll, ray count known exactly): flops per ray x rays / duration
+            kernel = "k_wf_extend"
+            achieved = extend_flops_per_ray(args.workload) * top_units / (top_ms / 1e3) / 1e12
+            per_launch = {"kernel": kernel, "sampled_launches": top_launches,
+                          "avg_launch_us": 1e3 * top_ms / top_launches,
+                          "avg_rays_per_launch": top_units / top_launches,
+                          "grays_per_s": top_units / (top_ms / 1e3) / 1e9,
+                          "flops_per_ray": extend_flops_per_ray(args.workload),
+                          "algorithmic_bytes_per_ray": extend_bytes_per_ray(args.workload)}
+        else:
+            kernel, achieved, per_launch = "whole step", step_tflops, None
         line = {
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -308,15 +348,18 @@ def gpu_arm(args, wl, rank, world, local_rank):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak,
-                         "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
-                         "flops_per_path": fpp,
-                         "note": "compute roofline of north_star: algorithmic FLOPs per path "
-                                 "(tests/hostsim work counters) x paths per step / step time; peak = "
-                                 "148 SM x 128 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json "
-                                 "(no measured fp32 figure there); HBM/tensor do not bound this path"},
+                         "unit": "TFLOP/s", "frac": achieved / fp32_peak,
+                         "traffic": NCU_TRAFFIC.get(args.workload) if wavefront else None,
+                         "kernel": kernel, "per_launch": per_launch,
+                         "whole_step": {"achieved": step_tflops, "frac": step_tflops / fp32_peak,
+                                        "flops_per_path": fpp},
+                         "note": "compute roofline of north_star (FP32 peak / algorithmic flops; "
+                                 "HBM and tensor cores do not bound this path): algorithmic work from "
+                                 "tests/hostsim counters; peak = 148 SM x 128 lanes x 2 x sm_max_mhz "
+                                 "of MEASURED_PEAKS.json, which holds no fp32 figure; traffic = ncu "
+                                 "dram bytes of one full-occupancy launch (profiles/)"},
             "reduce_ms": reduce_ms, "image_mean": image_mean,
             "host_build_s": host_build_s, "scene_upload_s": upload_s,
-            "first_extend_kernel_ms": float(np.mean(top_ms)) if args.pipeline != "mega" else None,
         }
         if world == 1 and not args.no_cpu_baseline:
             info = run_reference_cpu(wl, 8)

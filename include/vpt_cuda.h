@@ -201,13 +201,16 @@ typedef struct vpt_state vpt_state; /* device-resident accumulation image + rngs
 /* per-call device statistics, filled by vpt_cuda_trace_samples */
 typedef struct vpt_trace_stats {
   float    device_ms;       /* CUDA-event time of all kernels of the last call */
-  float    top_kernel_ms;   /* CUDA-event time of the dominant kernel(s) of the last call */
+  float    top_kernel_ms;   /* summed CUDA-event time of the SAMPLED launches of the dominant
+                               kernel (k_wf_extend: one launch per counter poll; the whole
+                               call for the megakernel) */
   int32_t  kernel_launches; /* kernels launched by the last call */
-  int32_t  reserved;
+  int32_t  top_kernel_launches; /* how many launches top_kernel_ms covers */
   uint64_t paths;           /* camera paths completed by the last call */
   uint64_t rays_extend;     /* closest-hit scene traversals */
   uint64_t rays_lightpdf;   /* instance-targeted traversals */
   uint64_t sdf_evals;       /* scene sdf evaluations */
+  uint64_t top_kernel_units; /* rays (paths for the megakernel) those sampled launches processed */
 } vpt_trace_stats;
 
 int  vpt_cuda_device_count(void);

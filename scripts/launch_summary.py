@@ -14,7 +14,7 @@ for r in rows[start + 1:]:
     d = launches.setdefault(int(r[iid]), {"k": r[ik].split("(")[0].replace("void ", "").replace("vpt::", ""),
                                           "grid": int(r[ig].strip("()").split(",")[0])})
     d[r[im]] = float(r[iv].replace(",", ""))
-tot = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0])
+tot = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0, 0.0])
 for d in launches.values():
     t = tot[d["k"]]
     t[0] += 1
@@ -22,12 +22,13 @@ for d in launches.values():
     inst = d.get("smsp__inst_executed.sum", 0.0)
     t[2] += inst
     t[3] += inst * d.get("smsp__thread_inst_executed_per_inst_executed.ratio", 0.0)
+    t[4] += d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)
 allt = sum(t[1] for t in tot.values())
 print(f"{len(launches)} launches, {allt / 1e6:.2f} ms of kernel time (serialised, cold cache, under ncu)")
-print(f"{'kernel':28s} {'n':>5s} {'ms':>9s} {'share':>7s} {'us/launch':>10s} {'lanes/inst':>10s}")
+print(f"{'kernel':28s} {'n':>5s} {'ms':>9s} {'share':>7s} {'us/launch':>10s} {'lanes/inst':>10s} {'dram/launch':>12s}")
 for k, t in sorted(tot.items(), key=lambda kv: -kv[1][1]):
     print(f"{k:28s} {t[0]:5d} {t[1] / 1e6:9.2f} {100 * t[1] / allt:6.1f}% {t[1] / t[0] / 1e3:10.1f} "
-          f"{(t[3] / t[2] if t[2] else 0):10.2f}")
+          f"{(t[3] / t[2] if t[2] else 0):10.2f} {t[4] / t[0]:12.3g}")
 print("\nper iteration (every %d): extend grid, us extend/shade/lightpdf, lanes extend/shade/lightpdf" % every)
 it, cur = [], None
 for d in launches.values():

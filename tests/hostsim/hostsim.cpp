@@ -204,7 +204,8 @@ int main(int argc, const char** argv) {
         per_path[i] = (float)(v[i] / paths);
         printf(" %s=%.3f", names[i], per_path[i]);
       }
-      printf("\n");
+      printf(" iq_box_tests=%.3f iq_tri_tests=%.3f\n", g_work.iq_box_tests / paths,
+          g_work.iq_tri_tests / paths);
       out.add_f32("work_per_path", {12}, per_path);
     }
     printf("hostsim: %dx%d %d spp shader=%s %.3f s\n", state.width, state.height, params.samples,

@@ -40,9 +40,10 @@ class Params(C.Structure):
 
 class TraceStats(C.Structure):
     _fields_ = [("device_ms", C.c_float), ("top_kernel_ms", C.c_float),
-                ("kernel_launches", C.c_int32), ("reserved", C.c_int32),
+                ("kernel_launches", C.c_int32), ("top_kernel_launches", C.c_int32),
                 ("paths", C.c_uint64), ("rays_extend", C.c_uint64),
-                ("rays_lightpdf", C.c_uint64), ("sdf_evals", C.c_uint64)]
+                ("rays_lightpdf", C.c_uint64), ("sdf_evals", C.c_uint64),
+                ("top_kernel_units", C.c_uint64)]
 
 
 BVH_NODE_DTYPE = np.dtype([("bbox_min", np.float32, 3), ("bbox_max", np.float32, 3),

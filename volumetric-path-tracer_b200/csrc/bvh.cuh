@@ -188,8 +188,15 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
 // Instance-targeted query (yocto_bvh.cpp:874-881), used by the light pdf.
 VPT_FN hit_t intersect_instance(const DScene& sc, int instance, const ray3& ray, stack_t st) {
   VPT_WORK(instance_queries, 1);
+#if defined(VPT_WORK_COUNTERS) && !defined(__CUDACC__)
+  // share of the box / primitive tests spent in light-pdf queries (run hostsim with --threads 1)
+  long long b0 = g_work.box_tests, t0 = g_work.tri_tests;
+#endif
   auto h     = traverse(sc, ~instance, ray, st);
   h.instance = instance;
+#if defined(VPT_WORK_COUNTERS) && !defined(__CUDACC__)
+  g_work.iq_box_tests += g_work.box_tests - b0, g_work.iq_tri_tests += g_work.tri_tests - t0;
+#endif
   return h;
 }
 

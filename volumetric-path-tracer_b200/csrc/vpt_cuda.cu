@@ -371,9 +371,13 @@ int vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params*
   VPT_CUDA_TRY(cudaEventElapsedTime(&ms, state->ev0, state->ev1));
   state->samples += todo;
   state->stats.device_ms       = ms;
-  if (state->stats.top_kernel_ms == 0) state->stats.top_kernel_ms = ms;
   state->stats.kernel_launches = launches;
   state->stats.paths           = (uint64_t)todo * state->width * state->height;
+  if (state->stats.top_kernel_launches == 0) {  // megakernel: the call is the kernel
+    state->stats.top_kernel_ms       = ms;
+    state->stats.top_kernel_launches = 1;
+    state->stats.top_kernel_units    = state->stats.paths;
+  }
   return VPT_OK;
 }
 

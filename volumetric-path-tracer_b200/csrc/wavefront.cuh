@@ -17,7 +17,7 @@
 // so many samples run per launch without a host round trip. Queues hold slot
 // ids and are compacted with warp-aggregated appends: __ballot_sync + __popc
 // give each lane its rank, one atomicAdd per warp reserves the range.
-// Per-slot state is SoA of 16-byte records (coalesced 128-bit loads / stores).
+// Per-slot state is one contiguous 160-byte record (see wf_view).
 //
 // Between extend and shade the queue is counting-sorted by shade class (miss,
 // inside-a-volume, surface material id): k_wf_extend takes a rank inside its
@@ -53,9 +53,30 @@ struct wf_counters {
   int                class_count[wf_classes];
 };
 
+// One 160-byte record per slot (5 aligned 32-byte sectors), fields in the order the
+// kernels touch them: extend reads the ray (sector 0) and writes the hit (sector 1);
+// shade / light-pdf read and write the rest. Keeping a slot's state contiguous matters
+// because the shade queue is class-sorted, i.e. slots are visited in scattered order:
+// nine separate SoA arrays cost nine half-used sectors per path (ncu r01: 1.0 GB of
+// DRAM traffic per k_wf_shade launch against 0.2 GB of state).
+enum : int {
+  wf_ray0 = 0,   // o.xyz, d.x
+  wf_ray1 = 1,   // d.yz, flags, remaining samples
+  wf_hit  = 2,   // instance, element, uv
+  wf_w1   = 3,   // weight.yz, vol_anisotropy, hit distance
+  wf_rad  = 4,   // radiance.xyz, weight.x
+  wf_mis  = 5,   // pending f.xyz, bsdf pdf
+  wf_vol0 = 6, wf_vol1 = 7, wf_vol2 = 8,  // density, scattering, emission of the current volume
+  wf_rng  = 9,   // the pixel's PCG32 state while the slot is live
+  wf_rec  = 10
+};
+
 // device pointers of one state's wavefront buffers
 struct wf_view {
-  f4 *        a0, *a1, *a2, *a3, *a4, *a5, *v0, *v1, *v2;
+  f4* rec;
+  __device__ __forceinline__ f4& at(int field, int slot) const {
+    return rec[(size_t)slot * wf_rec + field];
+  }
   int *       queue_ext[2], *queue_pdf;
   int *       queue_shade, *sort_key;  // class-sorted slots; (class << 24 | rank) per entry
   wf_counters* counters;
@@ -69,7 +90,7 @@ struct wavefront_buffers {
   cudaEvent_t  poll = nullptr, k0 = nullptr, k1 = nullptr;
   void release() {
     if (!capacity) return;
-    cudaFree(view.a0);
+    cudaFree(view.rec);
     cudaFree(view.queue_ext[0]);
     cudaFree(view.counters);
     if (host_counters) cudaFreeHost(host_counters);
@@ -81,12 +102,8 @@ struct wavefront_buffers {
   cudaError_t reserve(int slots) {
     if (capacity >= slots) return cudaSuccess;
     release();
-    f4*  block = nullptr;
-    auto e     = cudaMalloc(&block, sizeof(f4) * 9 * (size_t)slots);
+    auto e = cudaMalloc(&view.rec, sizeof(f4) * wf_rec * (size_t)slots);
     if (e != cudaSuccess) return e;
-    f4** arrays[9] = {&view.a0, &view.a1, &view.a2, &view.a3, &view.a4, &view.a5, &view.v0,
-        &view.v1, &view.v2};
-    for (int i = 0; i < 9; i++) *arrays[i] = block + (size_t)i * slots;
     int* q = nullptr;
     e      = cudaMalloc(&q, sizeof(int) * 5 * (size_t)slots);
     if (e != cudaSuccess) return e;
@@ -108,25 +125,29 @@ struct wavefront_buffers {
 // ---- per-slot state <-> registers -------------------------------------------
 constexpr int wf_bit_hit = 1 << 16, wf_bit_vol = 1 << 17, wf_bit_isec = 1 << 18;
 
+// `store_vol`: the volume fields only change when a path enters a volume
 template <int S>
 __device__ __forceinline__ void wf_store_path(const wf_view& w, int slot, const path_t& p,
-    int remaining) {
+    int remaining, bool store_vol) {
   int flags = (p.bounce & 0xffff) | (p.hit ? wf_bit_hit : 0) | (p.in_volume ? wf_bit_vol : 0);
-  w.a0[slot] = {p.o.x, p.o.y, p.o.z, p.d.x};
-  w.a1[slot] = {p.d.y, p.d.z, i2f(flags), i2f(remaining)};
-  w.a2[slot] = {p.radiance.x, p.radiance.y, p.radiance.z, p.weight.x};
-  w.a3[slot] = {p.weight.y, p.weight.z, p.vol_anisotropy, 0};
-  if (S == shader_volpathtrace) {
-    w.v0[slot] = {p.vol_density.x, p.vol_density.y, p.vol_density.z, p.vol_scattering.x};
-    w.v1[slot] = {p.vol_scattering.y, p.vol_scattering.z, p.vol_emission.x, p.vol_emission.y};
-    w.v2[slot] = {p.vol_emission.z, 0, 0, 0};
+  w.at(wf_ray0, slot) = {p.o.x, p.o.y, p.o.z, p.d.x};
+  w.at(wf_ray1, slot) = {p.d.y, p.d.z, i2f(flags), i2f(remaining)};
+  w.at(wf_rad, slot)  = {p.radiance.x, p.radiance.y, p.radiance.z, p.weight.x};
+  w.at(wf_w1, slot)   = {p.weight.y, p.weight.z, p.vol_anisotropy, 0};
+  if (S == shader_volpathtrace && store_vol) {
+    w.at(wf_vol0, slot) = {p.vol_density.x, p.vol_density.y, p.vol_density.z, p.vol_scattering.x};
+    w.at(wf_vol1, slot) = {p.vol_scattering.y, p.vol_scattering.z, p.vol_emission.x,
+        p.vol_emission.y};
+    w.at(wf_vol2, slot) = {p.vol_emission.z, 0, 0, 0};
   }
 }
 
+// volume fields are only meaningful (and only loaded) while the path is inside one
 template <int S>
 __device__ __forceinline__ void wf_load_path(const wf_view& w, int slot, path_t& p,
     int& remaining) {
-  auto a0 = w.a0[slot], a1 = w.a1[slot], a2 = w.a2[slot], a3 = w.a3[slot];
+  auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot), a2 = w.at(wf_rad, slot),
+       a3 = w.at(wf_w1, slot);
   p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
   int flags = f2i(a1.z);
   remaining = f2i(a1.w);
@@ -134,13 +155,19 @@ __device__ __forceinline__ void wf_load_path(const wf_view& w, int slot, path_t&
   p.in_volume = (flags & wf_bit_vol) != 0;
   p.radiance = {a2.x, a2.y, a2.z}, p.weight = {a2.w, a3.x, a3.y};
   p.vol_anisotropy = a3.z;
-  if (S == shader_volpathtrace) {
-    auto v0 = w.v0[slot], v1 = w.v1[slot], v2 = w.v2[slot];
+  p.vol_density = p.vol_scattering = p.vol_emission = {0, 0, 0};
+  if (S == shader_volpathtrace && p.in_volume) {
+    auto v0 = w.at(wf_vol0, slot), v1 = w.at(wf_vol1, slot), v2 = w.at(wf_vol2, slot);
     p.vol_density = {v0.x, v0.y, v0.z}, p.vol_scattering = {v0.w, v1.x, v1.y};
     p.vol_emission = {v1.z, v1.w, v2.x};
-  } else {
-    p.vol_density = p.vol_scattering = p.vol_emission = {0, 0, 0};
   }
+}
+
+__device__ __forceinline__ rng_t wf_load_rng(const wf_view& w, int slot) {
+  return *reinterpret_cast<const rng_t*>(&w.at(wf_rng, slot));
+}
+__device__ __forceinline__ void wf_store_rng(const wf_view& w, int slot, const rng_t& rng) {
+  *reinterpret_cast<rng_t*>(&w.at(wf_rng, slot)) = rng;
 }
 
 // warp-aggregated append of `slot` to a queue for the lanes with `push` set
@@ -182,9 +209,9 @@ __global__ void __launch_bounds__(wf_block)
       auto   rng = rngs[idx];
       path_t p;
       path_init(p, sample_camera(sc, prm, idx, rng));
-      wf_store_path<S>(w, slot, p, nsamples);
-      rngs[idx] = rng;
-      active    = true;
+      wf_store_path<S>(w, slot, p, nsamples, false);
+      wf_store_rng(w, slot, rng);
+      active = true;
     }
   }
   wf_push(w.queue_ext[0], &w.counters->count_ext[0], active, slot);
@@ -205,13 +232,13 @@ __global__ void __launch_bounds__(wf_block)
   if (tid >= count) return;
   int     slot = w.queue_ext[cur][tid];
   stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
-  auto    a0 = w.a0[slot], a1 = w.a1[slot];
+  auto    a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
   path_t  p;
   p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
   auto isec  = find_hit<S>(sc, prm, p, st);
-  w.a4[slot] = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
-  w.a3[slot].w = isec.distance;
-  w.a1[slot].z = i2f((f2i(a1.z) & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
+  w.at(wf_hit, slot)    = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
+  w.at(wf_w1, slot).w   = isec.distance;
+  w.at(wf_ray1, slot).z = i2f((f2i(a1.z) & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
   // shade class and the rank inside it
   int cls = 0;
   if (isec.hit) {
@@ -270,23 +297,25 @@ __global__ void __launch_bounds__(wf_block)
     path_t p;
     int    remaining;
     wf_load_path<S>(w, slot, p, remaining);
-    auto a4   = w.a4[slot];
-    auto isec = isect_t{(f2i(w.a1[slot].z) & wf_bit_isec) != 0, f2i(a4.x), f2i(a4.y),
-        {a4.z, a4.w}, w.a3[slot].w};
-    auto      rng = rngs[idx];
+    auto a4   = w.at(wf_hit, slot);
+    auto isec = isect_t{(f2i(w.at(wf_ray1, slot).z) & wf_bit_isec) != 0, f2i(a4.x), f2i(a4.y),
+        {a4.z, a4.w}, w.at(wf_w1, slot).w};
+    auto      rng     = wf_load_rng(w, slot);
+    bool      was_vol = p.in_volume;
     pending_t pd;
     auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);
     if (r == step_lightpdf) {
-      w.a5[slot] = {pd.f.x, pd.f.y, pd.f.z, pd.bpdf};
-      to_pdf     = true;
+      w.at(wf_mis, slot) = {pd.f.x, pd.f.y, pd.f.z, pd.bpdf};
+      to_pdf             = true;
     } else {
       bool alive = r == step_skip;
       if (r == step_continue) alive = bounce_tail<S>(prm, p, rng);
       if (!alive) alive = wf_finish<S>(sc, prm, idx, p, rng, image, remaining);
+      if (!alive) rngs[idx] = rng;  // slot done: hand the generator back to the state
       to_ext = alive;
     }
-    wf_store_path<S>(w, slot, p, remaining);
-    rngs[idx] = rng;
+    wf_store_path<S>(w, slot, p, remaining, p.in_volume && !was_vol);
+    wf_store_rng(w, slot, rng);
   }
   wf_push(w.queue_ext[cur ^ 1], &w.counters->count_ext[cur ^ 1], to_ext, slot);
   wf_push(w.queue_pdf, &w.counters->count_pdf, to_pdf, slot);
@@ -309,17 +338,18 @@ __global__ void __launch_bounds__(wf_block)
     path_t  p;
     int     remaining;
     wf_load_path<S>(w, slot, p, remaining);
-    auto a5 = w.a5[slot];
+    auto a5 = w.at(wf_mis, slot);
     auto pd = pending_t{p.o, p.d, {a5.x, a5.y, a5.z}, a5.w};
     // after shade_hit the next ray is (position, incoming): the pdf is taken along it
     auto lpdf = sample_lights_pdf(sc, p.o, p.d, prm.spheretrace_maxiter, st);
     apply_lightpdf(p, pd, lpdf);
-    auto rng   = rngs[idx];
+    auto rng   = wf_load_rng(w, slot);
     bool alive = bounce_tail<S>(prm, p, rng);
     if (!alive) alive = wf_finish<S>(sc, prm, idx, p, rng, image, remaining);
+    if (!alive) rngs[idx] = rng;
     to_ext = alive;
-    wf_store_path<S>(w, slot, p, remaining);
-    rngs[idx] = rng;
+    wf_store_path<S>(w, slot, p, remaining, false);
+    wf_store_rng(w, slot, rng);
   }
   wf_push(w.queue_ext[cur ^ 1], &w.counters->count_ext[cur ^ 1], to_ext, slot);
 }
@@ -344,7 +374,7 @@ __global__ void __launch_bounds__(wf_block)
     path_t  p;
     int     remaining;
     wf_load_path<S>(w, slot, p, remaining);
-    auto rng   = rngs[idx];
+    auto rng   = wf_load_rng(w, slot);
     auto alive = true;
     while (alive) {  // single exit
       auto      isec = find_hit<S>(sc, prm, p, st);
@@ -442,8 +472,11 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   k_wf_init<S><<<grid_all, wf_block>>>(scene.d, prm, w, rngs, slots, nsamples);
   *launches    = 1;
   int   active = slots, cur = 0;
-  float extend_ms = 0;
-  bool  timed     = false;
+  // the first extend launch after every poll is timed with CUDA events: its ray count
+  // (`active`) is known exactly, so the pairs give the dominant kernel's rays per second
+  double             top_ms = 0;
+  unsigned long long top_rays = 0;
+  int                top_launches = 0;
   int   drain_at  = wf_drain_threshold(slots);
   auto  trace     = wf_trace::open();
   if (smem > 48 * 1024) {
@@ -453,10 +486,10 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   while (active > 0) {
     int grid = (active + wf_block - 1) / wf_block;
     for (int it = 0; it < 8; it++) {
-      if (!timed) cudaEventRecord(wf.k0);
+      if (it == 0) cudaEventRecord(wf.k0);
       if (trace) trace->mark(grid);
       k_wf_extend<S><<<grid, wf_block, smem>>>(scene.d, prm, w, cur);
-      if (!timed) cudaEventRecord(wf.k1);
+      if (it == 0) cudaEventRecord(wf.k1);
       k_wf_sort<<<grid, wf_block>>>(w, cur);
       if (trace) trace->mark(grid);
       k_wf_shade<S><<<grid, wf_block>>>(scene.d, prm, w, image, rngs, cur);
@@ -465,17 +498,15 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (trace) trace->mark(grid);
       cur ^= 1;
       *launches += 4;
-      if (!timed) {
-        // the first (full-occupancy) extend launch is the per-kernel sample the
-        // bench reports next to the whole-call time
-        timed = true;
-      }
     }
     e = cudaMemcpyAsync(wf.host_counters, w.counters, sizeof(wf_counters), cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) return e;
     e = cudaEventRecord(wf.poll);
     if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
     if (e != cudaSuccess) return e;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, wf.k0, wf.k1) == cudaSuccess)
+      top_ms += ms, top_rays += (unsigned long long)active, top_launches += 1;
     active = wf.host_counters->count_ext[cur];
     if (active > 0 && active <= drain_at) {
       grid = (active + wf_block - 1) / wf_block;
@@ -489,8 +520,9 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     }
   }
   if (trace) trace->dump();
-  if (cudaEventElapsedTime(&extend_ms, wf.k0, wf.k1) == cudaSuccess)
-    stats->top_kernel_ms = extend_ms;
+  stats->top_kernel_ms       = (float)top_ms;
+  stats->top_kernel_launches = top_launches;
+  stats->top_kernel_units    = top_rays;
   stats->rays_extend   = wf.host_counters->rays_extend;
   stats->rays_lightpdf = wf.host_counters->rays_lightpdf;
   return cudaGetLastError();
