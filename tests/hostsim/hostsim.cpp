@@ -53,35 +53,71 @@ static void render(const DScene& sc, const DParams& prm, pathtrace_state& state,
   for (auto& t : threads) t.join();
 }
 
-// `hostsim --selftest-math N`: the fdlibm restatements in vmath.cuh (what the device
-// runs for atan / atan2 / acos) against this box's libm float functions, bit for bit,
-// on N random arguments per function plus the edge cases. Prints the mismatch count.
-static int selftest_math(long n) {
+// `hostsim --selftest-math N [stride]`: the restatements the DEVICE runs instead of libm
+// (vmath.cuh: atan / atan2 / acos from fdlibm; glibc_libm.cuh: sin / cos / exp / log / pow from
+// glibc's flt-32 algorithms) against this box's libm, bit for bit. Unary functions sweep every
+// `stride`-th float bit pattern (stride 1 = all 2^32), pow sweeps x over the same patterns for
+// the exponents the shaders use (5, 2.4) plus N random (x, y) pairs; atan2 takes N random pairs.
+// Also checks sincosf == (sinf, cosf). Prints the mismatch count; exit status 0 iff it is 0.
+static int selftest_math(long n, unsigned stride) {
   auto bits = [](float x) { uint32_t u; memcpy(&u, &x, 4); return u; };
   auto same = [&](float a, float b) { return bits(a) == bits(b) || (a != a && b != b); };
+  int  nthreads = (int)std::max(1u, std::thread::hardware_concurrency());
+  std::vector<long> bad(nthreads * 16, 0);
+  const char* names[9] = {"atanf", "acosf", "sinf", "cosf", "expf", "logf", "powf(x,5)", "powf(x,2.4)",
+      "sincosf"};
+  auto worker = [&](int t) {
+    long* b = &bad[t * 16];
+    uint64_t per = ((1ull << 32) / stride + nthreads - 1) / nthreads;
+    for (uint64_t k = per * t; k < per * (t + 1) && k * stride < (1ull << 32); k++) {
+      uint32_t u = (uint32_t)(k * stride);
+      float    x; memcpy(&x, &u, 4);
+      b[0] += !same(vatan(x), atanf(x));
+      b[1] += !same(vacos(x), acosf(x));
+      b[2] += !same(g_sinf(x), sinf(x));
+      b[3] += !same(g_cosf(x), cosf(x));
+      b[4] += !same(g_expf(x), expf(x));
+      b[5] += !same(g_logf(x), logf(x));
+      b[6] += !same(g_powf(x, 5.0f), powf(x, 5.0f));
+      b[7] += !same(g_powf(x, 2.4f), powf(x, 2.4f));
+      float sn, cs; sincosf(x, &sn, &cs);
+      b[8] += !same(sn, sinf(x)) + !same(cs, cosf(x));
+    }
+  };
+  std::vector<std::thread> threads;
+  for (int t = 0; t < nthreads; t++) threads.emplace_back(worker, t);
+  for (auto& t : threads) t.join();
+  long total = 0;
+  for (int f = 0; f < 9; f++) {
+    long c = 0;
+    for (int t = 0; t < nthreads; t++) c += bad[t * 16 + f];
+    printf("  %-12s %ld mismatches\n", names[f], c);
+    total += c;
+  }
   uint64_t s = 0x9e3779b97f4a7c15ull;
   auto next = [&]() { s ^= s << 13; s ^= s >> 7; s ^= s << 17; return (uint32_t)(s >> 16); };
   auto anyf = [&]() { uint32_t u = next(); float f; memcpy(&f, &u, 4); return f; };
   auto unit = [&]() { return ((int32_t)next()) / 2147483648.0f; };
-  long bad = 0;
-  float edges[] = {0.0f, -0.0f, 1.0f, -1.0f, 0.5f, -0.5f, 1e-30f, 1e30f, 3.4e38f, 0.4375f, 0.6875f,
-      1.1875f, 2.4375f, 33554432.0f, 33554431.0f, INFINITY, -INFINITY, NAN};
-  for (auto a : edges) {
-    bad += !same(vatan(a), atanf(a)) + !same(vacos(a), acosf(a));
-    for (auto b : edges) bad += !same(vatan2(a, b), atan2f(a, b));
-  }
+  long pairs = 0;
+  float edges[] = {0.0f, -0.0f, 1.0f, -1.0f, 0.5f, -0.5f, 2.0f, 3.0f, -3.0f, 1e-30f, 1e30f, 3.4e38f,
+      1e-45f, -1e-45f, 33554432.0f, INFINITY, -INFINITY, NAN};
+  for (auto a : edges)
+    for (auto b : edges) pairs += !same(vatan2(a, b), atan2f(a, b)) + !same(g_powf(a, b), powf(a, b));
   for (long i = 0; i < n; i++) {
     auto a = anyf(), b = anyf(), u = unit(), v = unit();
-    bad += !same(vatan(a), atanf(a)) + !same(vatan(u * 8), atanf(u * 8));
-    bad += !same(vatan2(a, b), atan2f(a, b)) + !same(vatan2(u, v), atan2f(u, v));
-    bad += !same(vacos(u), acosf(u)) + !same(vacos(a), acosf(a));
+    pairs += !same(vatan2(a, b), atan2f(a, b)) + !same(vatan2(u, v), atan2f(u, v));
+    pairs += !same(g_powf(a, b), powf(a, b)) + !same(g_powf(vabs(u), v * 8), powf(vabs(u), v * 8));
+    pairs += !same(g_powf(vabs(a), u * 40), powf(vabs(a), u * 40));
   }
-  printf("math selftest: %ld mismatches in %ld x 6 + edges\n", bad, n);
-  return bad == 0 ? 0 : 1;
+  printf("  %-12s %ld mismatches\n", "atan2f/powf pairs", pairs);
+  total += pairs;
+  printf("math selftest: %ld mismatches (stride %u, %ld random pairs)\n", total, stride, n);
+  return total == 0 ? 0 : 1;
 }
 
 int main(int argc, const char** argv) {
-  if (argc == 3 && std::string(argv[1]) == "--selftest-math") return selftest_math(atol(argv[2]));
+  if (argc >= 3 && std::string(argv[1]) == "--selftest-math")
+    return selftest_math(atol(argv[2]), argc > 3 ? (unsigned)atol(argv[3]) : 257u);
   if (argc < 3) {
     fprintf(stderr, "usage: hostsim scene.vptscene out.vptarch [opts]\n");
     return 2;

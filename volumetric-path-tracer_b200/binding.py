@@ -13,8 +13,10 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_CUDA_PATH = os.path.join(_HERE, "libvpt_cuda.so")
-LIB_HOST_PATH = os.path.join(_HERE, "libvpt_host.so")
+# VPT_LIB_DIR: load another build of the two libraries (kernel experiments); default in-tree
+_LIB_DIR = os.environ.get("VPT_LIB_DIR") or _HERE
+LIB_CUDA_PATH = os.path.join(_LIB_DIR, "libvpt_cuda.so")
+LIB_HOST_PATH = os.path.join(_LIB_DIR, "libvpt_host.so")
 
 SHADERS = ["volpathtrace", "pathtrace", "naive", "eyelight", "normal", "texcoord", "color",
            "implicit", "implicit_normal"]

@@ -109,23 +109,16 @@ VPT_FN float i2f(int i) {
 #endif
 }
 
-// libm entry points. glibc's float functions are (near-)correctly rounded;
-// rounding a double-precision evaluation to float reproduces them in all but
-// vanishingly rare cases, which is what the parity build (VPT_LIBM_F64) uses.
-// The throughput build calls CUDA's float functions.
-#if defined(__CUDA_ARCH__) && defined(VPT_LIBM_F64)
-VPT_FN float vsin(float a) { return (float)sin((double)a); }
-VPT_FN float vcos(float a) { return (float)cos((double)a); }
-VPT_FN float vlog(float a) { return (float)log((double)a); }
-VPT_FN float vexp(float a) { return (float)exp((double)a); }
-VPT_FN float vpow(float a, float b) { return (float)pow((double)a, (double)b); }
-#else
-VPT_FN float vsin(float a) { return sinf(a); }
-VPT_FN float vcos(float a) { return cosf(a); }
-VPT_FN float vlog(float a) { return logf(a); }
-VPT_FN float vexp(float a) { return expf(a); }
-VPT_FN float vpow(float a, float b) { return powf(a, b); }
-#endif
+// libm entry points. On the device sin / cos / log / exp / pow are glibc 2.39's own float
+// algorithms restated operation for operation (glibc_libm.cuh, included at the end of this
+// header), so that stochastic shaders replay the reference's random walk bit for bit. The host
+// build of this header (tests/hostsim) calls the box's libm, i.e. the real thing.
+// -DVPT_LIBM_CUDA falls back to CUDA's float functions (last-bit differences, ~2 % faster).
+VPT_FN float vsin(float a);
+VPT_FN float vcos(float a);
+VPT_FN float vlog(float a);
+VPT_FN float vexp(float a);
+VPT_FN float vpow(float a, float b);
 // atanf / atan2f / acosf: the reference links glibc 2.39, whose float versions
 // are the fdlibm float algorithms (sysdeps/ieee754/flt-32/s_atanf.c, e_atan2f.c,
 // e_acosf.c; not correctly rounded). They use only + - * / sqrt on floats, so
@@ -370,3 +363,5 @@ VPT_FN frame3 inverse_frame(const frame3& a, bool non_rigid) {
 }
 
 }  // namespace vpt
+
+#include "glibc_libm.cuh"

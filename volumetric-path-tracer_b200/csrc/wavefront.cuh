@@ -282,8 +282,11 @@ __global__ void __launch_bounds__(wf_block) k_wf_sort(wf_view w, int cur) {
   w.queue_shade[base[key >> 24] + (key & 0xffffff)] = w.queue_ext[cur][tid];
 }
 
+#if !defined(VPT_SHADE_BLOCKS)
+#define VPT_SHADE_BLOCKS 1
+#endif
 template <int S>
-__global__ void __launch_bounds__(wf_block)
+__global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
     k_wf_shade(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
         rng_t* __restrict__ rngs, int cur) {
   int  tid      = blockIdx.x * blockDim.x + threadIdx.x;
@@ -322,7 +325,7 @@ __global__ void __launch_bounds__(wf_block)
 }
 
 template <int S>
-__global__ void __launch_bounds__(wf_block)
+__global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
     k_wf_lightpdf(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
         rng_t* __restrict__ rngs, int cur) {
   extern __shared__ int stack_mem[];
