@@ -116,25 +116,45 @@ VPT_FN bool intersect_quad(f3 o, f3 d, float tmin, float tmax, f3 p0, f3 p1, f3 
 }
 
 constexpr int stack_sentinel = (int)0x80000000;
+#if !defined(VPT_TRAV_POPS)
+#define VPT_TRAV_POPS 8
+#endif
+constexpr int trav_pops = VPT_TRAV_POPS;
 
-// Closest hit below `first`: a scene node index, or ~instance for the
-// instance-targeted query. Uses stack slots [0, ...).
-VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) {
-  auto h = hit_t{-1, -1, {0, 0}, 0, false};
-  auto o = ray.o, d = ray.d;
-  auto tmin = ray.tmin, tmax = ray.tmax;
-  auto dinv = f3{1 / d.x, 1 / d.y, 1 / d.z};
-  bool plain = all_finite(dinv);
-  int  kind = -1;  // -1: scene level, else the element kind of the entered shape
-  int  inst = -1;
-  int  cur  = 0;
-  st.set(cur++, first);
-  VPT_GUARD_DECL(guard);
-  while (cur != 0) {
+// One ray's walk as resumable state, so that a plain loop (traverse) and the persistent
+// extend kernel (wavefront.cuh, which refills finished lanes between rounds) run the same code.
+struct trav_t {
+  f3    o, d, dinv;  // ray in the current space (world or the entered instance's)
+  f3    wdinv;       // 1 / d of the world-space ray, kept so leaving an instance costs no divisions
+  float tmin, tmax;
+  bool  plain, wplain;  // all of dinv finite (see intersect_box), for the current / world ray
+  int   kind;        // -1: scene level, else the element kind of the entered shape
+  int   inst, cur;
+  hit_t h;
+
+  // `first`: a scene node index, or ~instance for the instance-targeted query
+  VPT_FN void begin(int first, const ray3& ray, stack_t st) {
+    h = hit_t{-1, -1, {0, 0}, 0, false};
+    o = ray.o, d = ray.d;
+    tmin = ray.tmin, tmax = ray.tmax;
+    dinv  = f3{1 / d.x, 1 / d.y, 1 / d.z};
+    plain = all_finite(dinv);
+    wdinv = dinv, wplain = plain;
+    kind = -1, inst = -1, cur = 0;
+    st.set(cur++, first);
+  }
+  VPT_FN bool done() const { return cur == 0; }
+
+  // One round: pop until this lane holds a leaf, its stack is empty or it has popped
+  // `trav_pops` entries, then process the leaf if it has one. The bound keeps lanes that
+  // already hold a leaf from waiting on the lane with the longest descent (pops between
+  // leaves average ~10 and are roughly geometric, so the maximum over a warp was ~22 per
+  // round in ncu r01 while the mean lane needed 10); it changes the SIMT schedule only.
+  VPT_FN void round(const DScene& sc, const ray3& ray, stack_t st) {
     int lstart = 0, lnum = 0;
-    // descend: pop until this lane holds a leaf (or its stack is empty)
-    while (cur != 0 && lnum == 0) {
-      VPT_GUARD_STEP(2, guard, 30000);
+    int pops = trav_pops;
+    while (cur != 0 && lnum == 0 && pops != 0) {
+      pops--;
       int e = st.get(--cur);
       if (e >= 0) {
         auto n0 = ld4(sc.nodes + 2 * e), n1 = ld4(sc.nodes + 2 * e + 1);
@@ -153,9 +173,8 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
         }
       } else if (e == stack_sentinel) {
         o = ray.o, d = ray.d;
-        dinv  = f3{1 / d.x, 1 / d.y, 1 / d.z};
-        plain = all_finite(dinv);
-        kind  = -1;
+        dinv = wdinv, plain = wplain;
+        kind = -1;
       } else {
         inst = ~e;
         VPT_WORK(inst_transforms, 1);
@@ -164,8 +183,8 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
         auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
         auto root = f2i(c0.w);
         if (root >= 0) {
-          o    = transform_point(inv, ray.o);
-          d    = transform_vector(inv, ray.d);
+          o     = transform_point(inv, ray.o);
+          d     = transform_vector(inv, ray.d);
           dinv  = f3{1 / d.x, 1 / d.y, 1 / d.z};
           plain = all_finite(dinv);
           kind  = f2i(c1.w);
@@ -197,11 +216,18 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
       for (auto i = lnum - 1; i >= 0; i--) st.set(cur++, ~ld1(sc.scene_prims + lstart + i));
     }
   }
-#if defined(VPT_GUARD) && defined(__CUDA_ARCH__)
-  VPT_COUNT_ADD(5, guard >> 4);
-  VPT_COUNT_MAX(8, guard);
-#endif
-  return h;
+};
+
+// Closest hit below `first`. Uses stack slots [0, ...).
+VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) {
+  trav_t t;
+  t.begin(first, ray, st);
+  VPT_GUARD_DECL(guard);
+  while (!t.done()) {
+    VPT_GUARD_STEP(2, guard, 30000);
+    t.round(sc, ray, st);
+  }
+  return t.h;
 }
 
 // Instance-targeted query (yocto_bvh.cpp:874-881), used by the light pdf.

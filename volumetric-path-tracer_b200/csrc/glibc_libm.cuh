@@ -86,7 +86,7 @@ VPT_GFN float g_logf(float x) {
   if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
     if (ix * 2 == 0) return i2f((int)0xff800000);   // log(0) = -inf
     if (ix == 0x7f800000u) return x;                // log(inf) = inf
-    if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return (x - x) / 0.0f;  // nan
+    if ((ix & 0x80000000u) || ix * 2 >= 0xff000000u) return i2f(0x7fc00000);  // nan
     ix = g_asuint(x * 0x1p23f);                     // subnormal: normalise
     ix -= 23u << 23;
   }
@@ -135,7 +135,7 @@ VPT_GFN float g_powf(float x, float y) {
     }
     if (ix & 0x80000000u) {  // finite x < 0
       int yint = g_checkint(iy);
-      if (yint == 0) return (x - x) / 0.0f;
+      if (yint == 0) return i2f(0x7fc00000);
       if (yint == 1) sign_bias = 1ull << 16;  // SIGN_BIAS = 1 << (EXP2F_TABLE_BITS + 11)
       ix &= 0x7fffffffu;
     }
@@ -241,7 +241,7 @@ VPT_GFN float g_sincosf(float y, int want_cos) {
     x           = g_reduce_large(xi, n);
     q           = n + (int)(xi >> 31);  // signs and table include the argument's sign, parity does not
   } else {
-    return (y - y) / 0.0f;  // inf / nan
+    return i2f(0x7fc00000);  // inf / nan
   }
   double s = g_ld(g_sincosf_tab, q & 3);
   if (q & 2) p = g_sincosf_tab + 14;
