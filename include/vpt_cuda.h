@@ -69,7 +69,7 @@ typedef enum vpt_sdf_type {
 
 /* how the sample loop is scheduled on the device */
 typedef enum vpt_pipeline {
-  VPT_PIPELINE_AUTO      = 0, /* wavefront for the path shaders, megakernel for the debug shaders */
+  VPT_PIPELINE_AUTO      = 0, /* wavefront for pathtrace/volpathtrace/naive/implicit, megakernel for the debug shaders */
   VPT_PIPELINE_MEGA      = 1, /* one thread per pixel runs whole paths */
   VPT_PIPELINE_WAVEFRONT = 2  /* raygen -> extend -> shade -> light-pdf queues */
 } vpt_pipeline;

@@ -141,16 +141,41 @@ struct spheretrace_result {
   int   instance, sdf;
 };
 
-// spheretrace over the whole scene (yocto_pathtrace.cpp:289-307)
-VPT_FN spheretrace_result spheretrace(const DScene& sc, const ray3& ray, int maxiter) {
-  auto t = ray.tmin;
-  for (auto i = 0; i < maxiter && t < ray.tmax; ++i) {
-    auto p   = ray_point(ray, t);
-    auto res = eval_sdf_scene(sc, p, t);
-    if (vabs(res.result) < (flt_eps * t)) return {true, t, res.instance, res.sdf};
-    t += res.result;
+// spheretrace over the whole scene (yocto_pathtrace.cpp:289-307) as resumable state: the
+// persistent extend kernel advances every lane a few steps per round and refills the lanes
+// whose march is over (trip counts run from 1 to maxiter, so a fixed ray-per-lane launch
+// leaves most lanes idle: ncu r01 10 of 32).
+struct sphere_t {
+  float              t;
+  int                i;
+  bool               finished;
+  spheretrace_result r;
+  VPT_FN void begin(const ray3& ray) {
+    t = ray.tmin, i = 0, finished = false;
+    r = {false, flt_max, invalidid, invalidid};
   }
-  return {false, flt_max, invalidid, invalidid};
+  VPT_FN bool done() const { return finished; }
+  VPT_FN void step(const DScene& sc, const ray3& ray, int maxiter) {
+    if (i < maxiter && t < ray.tmax) {
+      auto p   = ray_point(ray, t);
+      auto res = eval_sdf_scene(sc, p, t);
+      if (vabs(res.result) < (flt_eps * t)) {
+        r        = {true, t, res.instance, res.sdf};
+        finished = true;
+      } else {
+        t += res.result;
+        ++i;
+      }
+    } else {
+      finished = true;
+    }
+  }
+};
+VPT_FN spheretrace_result spheretrace(const DScene& sc, const ray3& ray, int maxiter) {
+  sphere_t s;
+  s.begin(ray);
+  while (!s.done()) s.step(sc, ray, maxiter);
+  return s.r;
 }
 
 // spheretrace against one analytic sdf (yocto_pathtrace.cpp:267-286), light pdf

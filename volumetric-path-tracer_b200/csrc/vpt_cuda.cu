@@ -347,11 +347,10 @@ int vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params*
 
   bool path_shader = prm.shader == shader_volpathtrace || prm.shader == shader_pathtrace ||
                      prm.shader == shader_naive || prm.shader == shader_implicit;
-  // auto: the mesh path shaders run as a wavefront; sphere tracing is pure ALU with no
-  // traversal stage to split off and measures faster in the megakernel
+  // auto: the four Monte-Carlo shaders run as a wavefront (persistent extend with lane refill
+  // measures faster than the megakernel for BVH traversal and for sphere tracing alike)
   bool wavefront = params->pipeline == VPT_PIPELINE_WAVEFRONT ||
-                   (params->pipeline == VPT_PIPELINE_AUTO && path_shader &&
-                       prm.shader != shader_implicit);
+                   (params->pipeline == VPT_PIPELINE_AUTO && path_shader);
 
   VPT_CUDA_TRY(cudaEventRecord(state->ev0));
   int launches = 0;

@@ -262,18 +262,21 @@ __global__ void __launch_bounds__(wf_block)
   w.sort_key[tid] = (cls << 24) | (base + __popc(peers & ((1u << lane) - 1)));
 }
 
-// Persistent form of k_wf_extend for the mesh shaders. The grid is sized to the machine (one
-// resident set of warps); a warp claims queue entries for its idle lanes with one atomicAdd,
-// runs traversal rounds (trav_t::round: descend to a leaf, process it), retires the lanes whose
-// walk is over and refills them as soon as `wf_refill` lanes idle. A fixed ray-per-lane launch
-// keeps a warp busy until its slowest ray ends (ncu r01: 14.8 of 32 lanes live per round).
+// Persistent form of k_wf_extend. The grid is sized to the machine (one resident set of
+// warps); a warp claims queue entries for its idle lanes with one atomicAdd, runs rounds
+// (mesh shaders: trav_t::round = descend to a leaf and process it; SDF shaders: a few
+// sphere-tracing steps), retires the lanes whose walk is over and refills them as soon as
+// `wf_refill` lanes idle. A fixed ray-per-lane launch keeps a warp busy until its slowest ray
+// ends (ncu r01: 14.8 of 32 lanes live per traversal round, 10 of 32 in the SDF march).
 // Per ray the walk is the same sequence of operations, so hits are bit-identical.
-constexpr int wf_refill = 8;
+constexpr int wf_refill    = 8;
+constexpr int wf_sdf_steps = 4;
 
 template <int S>
 __global__ void __launch_bounds__(wf_block, 7)
     k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur) {
   extern __shared__ int stack_mem[];
+  constexpr bool sdf  = is_sdf_shader<S>();
   const unsigned full = 0xffffffffu;
   int     count = w.counters->count_ext[cur];
   int     lane  = threadIdx.x & 31;
@@ -283,13 +286,15 @@ __global__ void __launch_bounds__(wf_block, 7)
     w.counters->count_pdf          = 0;
     w.counters->rays_extend += (unsigned long long)count;
   }
-  trav_t t;
-  ray3   ray     = make_ray({0, 0, 0}, {0, 0, 1});
-  int    qidx    = 0, slot = 0, flags = 0;
-  bool   has_ray = false;
-  bool   more    = true;   // warp-uniform: the queue may still hold unclaimed entries
-  bool   running = true;   // warp-uniform, the only exit
-  t.cur          = 0;
+  trav_t   t;
+  sphere_t sp;
+  ray3     ray     = make_ray({0, 0, 0}, {0, 0, 1});
+  int      qidx    = 0, slot = 0, flags = 0;
+  bool     has_ray = false;
+  bool     more    = true;   // warp-uniform: the queue may still hold unclaimed entries
+  bool     running = true;   // warp-uniform, the only exit
+  t.cur       = 0;
+  sp.finished = true;
   while (running) {
     unsigned idle = __ballot_sync(full, !has_ray);
     if (more && (__popc(idle) >= wf_refill)) {
@@ -304,22 +309,41 @@ __global__ void __launch_bounds__(wf_block, 7)
         auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
         flags   = f2i(a1.z);
         ray     = make_ray({a0.x, a0.y, a0.z}, {a0.w, a1.x, a1.y});
-        t.begin(sc.scene_root, ray, st);
-        if (sc.scene_root < 0) t.cur = 0;  // no instances: every ray misses
+        if constexpr (sdf) {
+          sp.begin(ray);
+        } else {
+          t.begin(sc.scene_root, ray, st);
+          if (sc.scene_root < 0) t.cur = 0;  // no instances: every ray misses
+        }
         has_ray = true;
       }
     }
-    if (has_ray && !t.done()) t.round(sc, ray, st);
-    bool     retire   = has_ray && t.done();
+    if constexpr (sdf) {
+      for (int k = 0; k < wf_sdf_steps; k++)
+        if (has_ray && !sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
+    } else {
+      if (has_ray && !t.done()) t.round(sc, ray, st);
+    }
+    bool     retire   = has_ray && (sdf ? sp.done() : t.done());
     unsigned retiring = __ballot_sync(full, retire);
     if (retire) {
-      auto& h = t.h;
-      w.at(wf_hit, slot)    = {i2f(h.instance), i2f(h.element), h.uv.x, h.uv.y};
-      w.at(wf_w1, slot).w   = h.distance;
-      w.at(wf_ray1, slot).z = i2f((flags & ~wf_bit_isec) | (h.hit ? wf_bit_isec : 0));
+      isect_t isec;
+      if constexpr (sdf)
+        isec = {sp.r.hit, sp.r.instance, sp.r.sdf, {0, 0}, sp.r.dist};
+      else
+        isec = {t.h.hit, t.h.instance, t.h.element, t.h.uv, t.h.distance};
+      w.at(wf_hit, slot)    = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
+      w.at(wf_w1, slot).w   = isec.distance;
+      w.at(wf_ray1, slot).z = i2f((flags & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
       int cls = 0;
-      if (h.hit) {
-        int material = f2i(ld4(sc.inst_trav + 4 * h.instance + 3).w);
+      if (isec.hit) {
+        int material;
+        if constexpr (sdf)
+          material = isec.instance != invalidid
+                         ? f2i(ld4(sc.vol_instances + 4 * isec.instance + 2).w)
+                         : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
+        else
+          material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);
         cls = 2 + (material < wf_classes - 3 ? material : wf_classes - 3);
         if (S == shader_volpathtrace && (flags & wf_bit_vol)) cls = 1;
       }
@@ -561,7 +585,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   int                top_launches = 0;
   int   drain_at  = wf_drain_threshold(slots);
   // persistent extend (mesh shaders): as many blocks as the device keeps resident
-  bool persistent = !is_sdf_shader<S>() && !getenv("VPT_WF_NO_PERSISTENT");
+  bool persistent = !getenv("VPT_WF_NO_PERSISTENT");
   int  resident   = 0;
   if (persistent) {
     int per_sm = 0, device = 0, sms = 0;
