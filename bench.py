@@ -60,7 +60,7 @@ WORK = {
                       sdf_scene_evals=0, sdf_fn_evals=0, sdf_grid_evals=0, trilinear=0),
     "01_surface": dict(box_tests=49.44, tri_tests=9.19, inst_transforms=13.58, bounces=2.044,
                        sdf_scene_evals=0, sdf_fn_evals=0, sdf_grid_evals=0, trilinear=0),
-    "05_head1ss": dict(box_tests=260.0, tri_tests=30.0, inst_transforms=8.0, bounces=6.0,
+    "05_head1ss": dict(box_tests=61.12, tri_tests=7.17, inst_transforms=0.93, bounces=1.502,
                        sdf_scene_evals=0, sdf_fn_evals=0, sdf_grid_evals=0, trilinear=0),
     "06_gridsdf": dict(box_tests=0, tri_tests=0, inst_transforms=0, bounces=1.866,
                        sdf_scene_evals=143.89, sdf_fn_evals=366.74, sdf_grid_evals=576.62,
@@ -80,6 +80,7 @@ SM_COUNT, FP32_LANES = 148, 128
 EXTEND = {
     "03_volume": dict(box_tests=36.37, tri_tests=10.52, inst_transforms=6.06, prim_bytes=64),
     "01_surface": dict(box_tests=22.45, tri_tests=4.02, inst_transforms=4.90, prim_bytes=48),
+    "05_head1ss": dict(box_tests=40.69, tri_tests=4.78, inst_transforms=0.62, prim_bytes=48),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend launch, from
 # profiles/r01_ncu_full_sorted_pipeline.brief.txt (ncu --set full), per launch like `achieved`
