@@ -12,7 +12,7 @@
 // usage: ref_render <scene.vptscene> <out.vptarch> [--shader NAME]
 //        [--samples N] [--resolution R] [--bounces B] [--noimplicitmis]
 //        [--stmaxiter M] [--noparallel] [--rays rays.vptarch]
-//        [--instance K] [--dump-state] [--dump-host]
+//        [--instance K] [--dump-state] [--dump-host] [--camera N]
 #include <yocto/yocto_bvh.h>
 #include <yocto/yocto_scene.h>
 #include <yocto/yocto_sdfs.h>
@@ -79,6 +79,8 @@ int main(int argc, const char** argv) {
       params.resolution = std::stoi(next());
     else if (a == "--bounces")
       params.bounces = std::stoi(next());
+    else if (a == "--camera")
+      params.camera = std::stoi(next());
     else if (a == "--stmaxiter")
       params.spheretrace_maxiter = std::stoi(next());
     else if (a == "--noimplicitmis")

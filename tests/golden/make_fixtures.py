@@ -4,7 +4,7 @@
                       degenerates to a triangle), byte sRGB / byte linear / float
                       textures, a normal map, vertex colours, opacity < 1, a
                       non-rigid instance frame, an area light and a textured
-                      environment; two cameras (pinhole, thin lens)
+                      environment; four cameras (pinhole, thin lens, orthographic, portrait)
   sdf_small.vptscene  one 16^3 voxel-grid SDF instance plus one analytic SDF of every type
 
 The scenes are written from numpy alone (seeded), so they can be rebuilt
@@ -65,9 +65,10 @@ def lookat(eye, center, up=(0, 1, 0)):
     return f32(np.concatenate([x, y, z, np.asarray(eye, dtype=np.float64)]))
 
 
-def camera(eye, center, lens=0.05, film=0.036, aspect=1.5, aperture=0.0):
+def camera(eye, center, lens=0.05, film=0.036, aspect=1.5, aperture=0.0, orthographic=False):
     focus = float(np.linalg.norm(np.subtract(eye, center)))
-    return np.concatenate([lookat(eye, center), f32([0, lens, film, aspect, focus, aperture])])
+    return np.concatenate([lookat(eye, center),
+                           f32([float(orthographic), lens, film, aspect, focus, aperture])])
 
 
 def material(type_, color=(0, 0, 0), emission=(0, 0, 0), roughness=0.0, metallic=0.0, ior=1.5,
@@ -162,7 +163,9 @@ def build_mixed():
     rng = np.random.default_rng(20260311)
     a = {"meta": np.asarray([1, 0, 0, 0], np.int32)}
     a["cameras"] = f32(np.stack([camera((0.0, 1.0, 3.4), (0, 0.25, 0)),
-                                 camera((1.8, 1.2, 2.8), (0, 0.2, 0), aperture=0.02)]))
+                                 camera((1.8, 1.2, 2.8), (0, 0.2, 0), aperture=0.02),
+                                 camera((0.0, 1.5, 3.0), (0, 0.3, 0), lens=0.012, orthographic=True),
+                                 camera((-1.5, 0.8, 2.6), (0, 0.3, 0), aspect=0.75, aperture=0.01)]))
     # textures: 0 colour (byte sRGB), 1 normal map (byte linear), 2 environment (float),
     # 3 roughness (byte sRGB), 4 emission (float)
     checker = (np.indices((16, 16)).sum(0) % 2)[..., None]

@@ -136,6 +136,7 @@ int main(int argc, const char** argv) {
     } else if (a == "--samples") params.samples = std::stoi(next());
     else if (a == "--resolution") params.resolution = std::stoi(next());
     else if (a == "--bounces") params.bounces = std::stoi(next());
+    else if (a == "--camera") params.camera = std::stoi(next());
     else if (a == "--stmaxiter") params.spheretrace_maxiter = std::stoi(next());
     else if (a == "--noimplicitmis") params.noimplicit_mis = true;
     else if (a == "--rays") rays_file = next();

@@ -85,6 +85,21 @@ def test_device_code_on_host_matches_golden(vpt, hostsim, tmp_path, case):
     assert np.array_equal(got["rngs_after"], ref["rngs_after"])
 
 
+@pytest.mark.parametrize("camera", [1, 2, 3])
+def test_cameras_on_host_match_oracle(vpt, hostsim, tmp_path, camera):
+    """Thin-lens, orthographic and portrait cameras: device headers on the host vs the live oracle."""
+    if not util.have_ref():
+        pytest.skip("oracle/_ref/ref_render not built")
+    a, b = str(tmp_path / "a.vptarch"), str(tmp_path / "b.vptarch")
+    args = ("--shader", "pathtrace", "--samples", 2, "--resolution", 64, "--camera", camera)
+    run_tool(util.REF_RENDER, "mixed", a, *args, "--dump-state")
+    run_tool(hostsim, "mixed", b, *args)
+    ref, got = vpt.archive.load(a), vpt.archive.load(b)
+    assert ref["image_sum"].shape == got["image_sum"].shape
+    assert not util.bit_mismatch(got["image_sum"], ref["image_sum"]).any()
+    assert np.array_equal(got["rngs_after"], ref["rngs_after"])
+
+
 @pytest.mark.parametrize("scene", ["mixed", "sdf_small"])
 def test_first_hits_on_host_match_golden(vpt, hostsim, tmp_path, scene):
     rays = util.camera_rays(0, 0, np.random.default_rng(7), 4096)

@@ -170,6 +170,27 @@ def test_stochastic_shaders_replay_the_reference_bit_for_bit(vpt, scenes, scene,
     r.close()
 
 
+@pytest.mark.parametrize("camera", [1, 2, 3])
+@pytest.mark.parametrize("shader", ["color", "pathtrace"])
+def test_cameras_bit_exact(vpt, scenes, camera, shader):
+    """eval_camera (yocto_scene.cpp:67-102): thin lens, orthographic and portrait (aspect < 1,
+    transposed make_state size) cameras of the `mixed` fixture."""
+    sc = scenes("mixed")
+    spp, res = 2, 128
+    ref = util.oracle_render(vpt, "mixed", shader, spp, res, extra_args=("--camera", str(camera)))
+    if ref is None:
+        pytest.skip("oracle binary absent")
+    r = vpt.binding.Render(sc, vpt.binding.make_params(shader=shader, samples=spp, resolution=res,
+                                                       camera=camera))
+    r.trace(spp)
+    assert ref["image_sum"].shape[:2] == (r.height, r.width)
+    if camera == 3:
+        assert r.height == res and r.width < res
+    assert not util.bit_mismatch(r.image(normalized=False), ref["image_sum"]).any()
+    assert np.array_equal(r.rngs(), ref["rngs_after"])
+    r.close()
+
+
 def test_full_size_render_is_bit_exact(vpt, scenes):
     """BASELINE.json's headline configuration at its full size (03_volume, volpathtrace,
     1280x533, 64 bounces) for as many samples as the oracle renders in a few seconds."""
