@@ -73,7 +73,7 @@ FLOPS = dict(box_tests=26, tri_tests=52, inst_transforms=30, bounces=300, sdf_sc
              sdf_fn_evals=45, sdf_grid_evals=43, trilinear=30)
 SM_COUNT, FP32_LANES = 148, 128
 
-# The dominant kernel is k_wf_extend (one closest-hit query per queued ray). Its algorithmic
+# The dominant kernel is k_wf_extend_persistent (one closest-hit query per queued ray). Its algorithmic
 # work per RAY: the counters above minus the share spent in light-pdf instance queries
 # (hostsim iq_* counters), divided by the rays per path; bytes = nodes 32 B, primitives 48/64 B,
 # instance records 64 B, plus the ray read (32 B) and hit write (24 B) that must touch HBM.
@@ -82,9 +82,9 @@ EXTEND = {
     "01_surface": dict(box_tests=22.45, tri_tests=4.02, inst_transforms=4.90, prim_bytes=48),
     "05_head1ss": dict(box_tests=40.69, tri_tests=4.78, inst_transforms=0.62, prim_bytes=48),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend launch, from
-# profiles/r01_ncu_full_sorted_pipeline.brief.txt (ncu --set full), per launch like `achieved`
-NCU_TRAFFIC = {"03_volume": 32.8e6 + 12.4e6}
+# dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend_persistent
+# launch, from profiles/r01_ncu_full_final.brief.txt (ncu --set full), per launch like `achieved`
+NCU_TRAFFIC = {"03_volume": 93.0e6 + 27.5e6}
 
 
 def extend_flops_per_ray(name):
@@ -329,7 +329,7 @@ def gpu_arm(args, wl, rank, world, local_rank):
         if wavefront:
             # dominant kernel, timed live with CUDA events on its own stream (one launch per
             # counter poll, ray count known exactly): flops per ray x rays / duration
-            kernel = "k_wf_extend"
+            kernel = "k_wf_extend_persistent"
             achieved = extend_flops_per_ray(args.workload) * top_units / (top_ms / 1e3) / 1e12
             per_launch = {"kernel": kernel, "sampled_launches": top_launches,
                           "avg_launch_us": 1e3 * top_ms / top_launches,

@@ -20,9 +20,11 @@
 #if defined(__CUDACC__)
 #define VPT_TABLE static __device__ const
 #define VPT_GFN __device__ __forceinline__
+#define VPT_GCALL __device__ __noinline__  // the five entry points are real calls: ~10 call sites
 #else
 #define VPT_TABLE static const
 #define VPT_GFN inline
+#define VPT_GCALL inline
 #endif
 
 namespace vpt {
@@ -55,7 +57,7 @@ VPT_GFN double g_ld(const double* t, int i) {
 }
 
 // ---- expf (e_expf.c) ---------------------------------------------------------------
-VPT_GFN float g_expf(float x) {
+VPT_GCALL float g_expf(float x) {
   double   xd     = (double)x;
   unsigned abstop = (g_asuint(x) >> 20) & 0x7ff;
   if (abstop > 0x42a) {  // |x| >= 88 or nan
@@ -80,7 +82,7 @@ VPT_GFN float g_expf(float x) {
 }
 
 // ---- logf (e_logf.c) ---------------------------------------------------------------
-VPT_GFN float g_logf(float x) {
+VPT_GCALL float g_logf(float x) {
   unsigned ix = g_asuint(x);
   if (ix == 0x3f800000u) return 0.0f;
   if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u) {
@@ -116,7 +118,7 @@ VPT_GFN int g_checkint(unsigned iy) {  // 0: not an integer, 1: odd, 2: even
   return 2;
 }
 VPT_GFN bool g_zeroinfnan(unsigned ix) { return 2 * ix - 1 >= 2u * 0x7f800000u - 1; }
-VPT_GFN float g_powf(float x, float y) {
+VPT_GCALL float g_powf(float x, float y) {
   unsigned long long sign_bias = 0;
   unsigned ix = g_asuint(x), iy = g_asuint(y);
   if (ix - 0x00800000u >= 0x7f800000u - 0x00800000u || g_zeroinfnan(iy)) {
@@ -223,7 +225,7 @@ VPT_GFN double g_reduce_large(unsigned xi, int& n) {
   return (double)(long long)res0 * g_pi63[0];
 }
 // want_cos = 0: sinf, 1: cosf
-VPT_GFN float g_sincosf(float y, int want_cos) {
+VPT_GCALL float g_sincosf(float y, int want_cos) {
   double   x      = (double)y;
   unsigned abstop = (g_asuint(y) >> 20) & 0x7ff;
   const double* p = g_sincosf_tab;
