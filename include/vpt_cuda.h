@@ -239,6 +239,13 @@ int  vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params
          int nsamples);
 int  vpt_cuda_get_trace_stats(const vpt_state* state, vpt_trace_stats* stats);
 
+/* Output stage on the device: get_render (yocto_pathtrace.cpp:1105-1116:
+ * sum * (1 / samples)) followed by what save_image does for 8-bit formats
+ * (yocto_sceneio.cpp:523-529: rgb_to_srgb + float_to_byte, alpha linear); n = width*height*4
+ * bytes; `samples` is the divisor (pass 0 for the state's own count; after a cross-GPU reduce it is
+ * the total over ranks). A quarter of the float image crosses PCIe; bytes equal the reference's. */
+int  vpt_cuda_download_srgb8(vpt_state* state, int samples, uint8_t* rgba, size_t n);
+
 /* un-normalised sums, n = width*height*4 floats (get_render divides by samples) */
 int  vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n);
 int  vpt_cuda_download_rngs(vpt_state* state, uint64_t* rngs, size_t n);

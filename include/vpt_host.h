@@ -49,6 +49,8 @@ int  vpth_render_samples(vpth_render* render, int nsamples);
 int  vpth_render_done_samples(const vpth_render* render);
 /* normalized != 0: get_render (sum / samples); else the raw sums */
 int  vpth_render_get_image(vpth_render* render, float* rgba, int normalized);
+/* device-side output stage: 8-bit sRGB RGBA of the current render, [height][width][4] */
+int  vpth_render_get_srgb8(vpth_render* render, uint8_t* rgba);
 int  vpth_render_stats(const vpth_render* render, vpt_trace_stats* stats);
 /* device pointer of the accumulation image (for a collective), or null */
 void* vpth_render_device_image(vpth_render* render);

@@ -14,6 +14,7 @@
 //        [--stmaxiter M] [--noparallel] [--rays rays.vptarch]
 //        [--instance K] [--dump-state] [--dump-host] [--camera N]
 #include <yocto/yocto_bvh.h>
+#include <yocto/yocto_image.h>
 #include <yocto/yocto_scene.h>
 #include <yocto/yocto_sdfs.h>
 #include <yocto_pathtrace/yocto_pathtrace.h>
@@ -215,6 +216,12 @@ int main(int argc, const char** argv) {
     if (dump_state) {
       out.add("rngs_after", vpt::dt_u64, {(uint64_t)state.rngs.size(), 2},
           state.rngs.data());
+      // what save_image encodes for an 8-bit format (yocto_sceneio.cpp:523-529):
+      // rgb_to_srgb + float_to_byte of the get_render image
+      auto ldr = std::vector<vec4b>{};
+      rgb_to_srgb(ldr, image.pixels);
+      out.add("image_srgb8", vpt::dt_u8, {(uint64_t)state.height, (uint64_t)state.width, 4},
+          ldr.data());
     }
     int meta[4] = {state.width, state.height, state.samples,
         (int)std::thread::hardware_concurrency()};

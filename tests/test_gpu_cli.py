@@ -64,3 +64,33 @@ def test_cli_rejects_what_the_reference_rejects(tmp_path):
     r = subprocess.run([CLI, "--scene", util.scene_path("mixed"), "--output", str(tmp_path / "x.pfm"),
                         "--interactive"], capture_output=True, text=True)
     assert r.returncode != 0 and "unavailable on this box" in (r.stdout + r.stderr)
+
+
+@pytest.mark.parametrize("scene,shader", [("mixed", "pathtrace"), ("mixed", "color"), ("sdf_small", "implicit")])
+def test_device_output_stage_equals_reference_bytes(vpt, tmp_path, scene, shader):
+    """get_render + rgb_to_srgb + float_to_byte on the device. The bytes equal what
+    the reference's save_image encodes for an 8-bit format (rgb_to_srgb(vector<vec4b>&, ...),
+    yocto_image.cpp:870-874), through the binding and in the CLI's .ppm output."""
+    spp, res = 4, 96
+    ref = util.oracle_render(vpt, scene, shader, spp, res)
+    if ref is None or "image_srgb8" not in ref:
+        pytest.skip("oracle binary absent")
+    sc = vpt.binding.Scene(util.scene_path(scene))
+    r = vpt.binding.Render(sc, vpt.binding.make_params(shader=shader, samples=spp, resolution=res))
+    r.trace(spp)
+    got = r.image_srgb8()
+    r.close()
+    sc.close()
+    assert got.shape == ref["image_srgb8"].shape
+    assert np.array_equal(got, ref["image_srgb8"])
+    assert got[..., :3].std() > 5, "image should not be flat"
+    out = str(tmp_path / "o.ppm")
+    c = subprocess.run([CLI, "--scene", util.scene_path(scene), "--output", out, "--shader", shader,
+                        "--samples", str(spp), "--resolution", str(res)], capture_output=True, text=True)
+    assert c.returncode == 0, c.stdout + c.stderr
+    with open(out, "rb") as f:
+        assert f.readline().strip() == b"P6"
+        w, h = map(int, f.readline().split())
+        assert f.readline().strip() == b"255"
+        rgb = np.frombuffer(f.read(), dtype=np.uint8).reshape(h, w, 3)
+    assert np.array_equal(rgb, ref["image_srgb8"][..., :3])

@@ -84,7 +84,9 @@ static bool save_png(const std::string& path, int w, int h, const std::vector<ui
 }
 
 // save_image by extension (yocto_sceneio.cpp:509-591): ldr formats get rgb_to_srgb + 8 bit
-static bool save_image(const std::string& path, const color_image& image, std::string& error) {
+// `srgb8`: the 8-bit image already converted on the device (get_render_srgb8), or empty
+static bool save_image(const std::string& path, const color_image& image, std::string& error,
+    const std::vector<uint8_t>& srgb8 = {}) {
   auto ext = path.substr(path.find_last_of('.') == std::string::npos ? path.size()
                                                                       : path.find_last_of('.'));
   auto w = image.width, h = image.height;
@@ -112,13 +114,16 @@ static bool save_image(const std::string& path, const color_image& image, std::s
     fclose(fs);
     return true;
   }
-  auto bytes = std::vector<uint8_t>((size_t)w * h * 4);
-  for (size_t i = 0; i < (size_t)w * h; i++) {
-    auto& p          = image.pixels[i];
-    bytes[4 * i + 0] = float_to_byte(rgb_to_srgb(p.x));
-    bytes[4 * i + 1] = float_to_byte(rgb_to_srgb(p.y));
-    bytes[4 * i + 2] = float_to_byte(rgb_to_srgb(p.z));
-    bytes[4 * i + 3] = float_to_byte(p.w);
+  auto bytes = srgb8;
+  if (bytes.size() != (size_t)w * h * 4) {
+    bytes.resize((size_t)w * h * 4);
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+      auto& p          = image.pixels[i];
+      bytes[4 * i + 0] = float_to_byte(rgb_to_srgb(p.x));
+      bytes[4 * i + 1] = float_to_byte(rgb_to_srgb(p.y));
+      bytes[4 * i + 2] = float_to_byte(rgb_to_srgb(p.z));
+      bytes[4 * i + 3] = float_to_byte(p.w);
+    }
   }
   if (ext == ".png") {
     if (!save_png(path, w, h, bytes)) return error = "cannot create " + path, false;
@@ -222,7 +227,10 @@ int main(int argc, const char** argv) {
     printf("\nrender: %.3f s, %.2f Mpaths/s (%dx%d, %d spp, %s)\n", seconds,
         (double)state.width * state.height * state.samples / seconds / 1e6, state.width,
         state.height, state.samples, pathtrace_shader_names[(int)params.shader].c_str());
-    if (!save_image(outname, render, error)) print_fatal(error);
+    auto ldr = outname.size() > 4 && (outname.substr(outname.size() - 4) == ".png" ||
+                                         outname.substr(outname.size() - 4) == ".ppm");
+    if (!save_image(outname, render, error, ldr ? get_render_srgb8(state) : std::vector<uint8_t>{}))
+      print_fatal(error);
     printf("saved %s\n", outname.c_str());
   } catch (std::exception& e) {
     print_fatal(e.what());

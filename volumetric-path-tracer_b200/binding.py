@@ -222,6 +222,12 @@ class Render:
         _check(self._host.vpth_render_get_image(self._h, _fptr(out), int(normalized)))
         return out
 
+    def image_srgb8(self) -> np.ndarray:
+        """Output stage on the device: get_render + rgb_to_srgb + float_to_byte -> [h, w, 4] uint8."""
+        out = np.zeros((self.height, self.width, 4), dtype=np.uint8)
+        _check(self._host.vpth_render_get_srgb8(self._h, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
     def stats(self) -> TraceStats:
         s = TraceStats()
         _check(self._host.vpth_render_stats(self._h, C.byref(s)))

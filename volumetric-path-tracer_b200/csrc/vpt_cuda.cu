@@ -194,6 +194,23 @@ static cudaError_t dispatch_mega(const vpt_scene* scene, vpt_state* state, const
   }
 }
 
+// get_render + rgb_to_srgb + float_to_byte (yocto_color.h:207-231), one thread per pixel
+__device__ __forceinline__ float out_rgb_to_srgb(float rgb) {
+  return (rgb <= 0.0031308f) ? 12.92f * rgb : (1 + 0.055f) * vpt::vpow(rgb, 1 / 2.4f) - 0.055f;
+}
+__device__ __forceinline__ unsigned char out_float_to_byte(float a) {
+  return (unsigned char)vpt::vclamp((int)(a * 256), 0, 255);
+}
+__global__ void k_output_srgb8(const vpt::f4* __restrict__ image, uchar4* __restrict__ out,
+    size_t pixels, float scale) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= pixels) return;
+  auto p = image[idx] * scale;
+  out[idx] = make_uchar4(out_float_to_byte(out_rgb_to_srgb(p.x)),
+      out_float_to_byte(out_rgb_to_srgb(p.y)), out_float_to_byte(out_rgb_to_srgb(p.z)),
+      out_float_to_byte(p.w));
+}
+
 // ---------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------
@@ -391,6 +408,23 @@ int vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n) {
   size_t want = (size_t)state->width * state->height * 4;
   if (n != want) return set_error(VPT_ERR_INVALID, "image should have the same size");
   VPT_CUDA_TRY(cudaMemcpy(rgba, state->image, want * sizeof(float), cudaMemcpyDeviceToHost));
+  return VPT_OK;
+}
+
+int vpt_cuda_download_srgb8(vpt_state* state, int samples, uint8_t* rgba, size_t n) {
+  if (auto r = require_device()) return r;
+  if (!state || !rgba) return set_error(VPT_ERR_INVALID, "null argument");
+  size_t pixels = (size_t)state->width * state->height;
+  if (n != pixels * 4) return set_error(VPT_ERR_INVALID, "image should have the same size");
+  if (samples <= 0) samples = state->samples;
+  if (samples <= 0) return set_error(VPT_ERR_INVALID, "nothing rendered yet");
+  uchar4* dev = nullptr;
+  VPT_CUDA_TRY(cudaMalloc(&dev, pixels * sizeof(uchar4)));
+  k_output_srgb8<<<(unsigned)((pixels + 255) / 256), 256>>>(state->image, dev, pixels,
+      1.0f / (float)samples);
+  auto e = cudaMemcpy(rgba, dev, pixels * sizeof(uchar4), cudaMemcpyDeviceToHost);
+  cudaFree(dev);
+  if (e != cudaSuccess) return cuda_fail(e, "download_srgb8");
   return VPT_OK;
 }
 

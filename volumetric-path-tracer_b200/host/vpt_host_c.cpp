@@ -242,6 +242,14 @@ int vpth_render_get_image(vpth_render* r, float* rgba, int normalized) {
   });
 }
 
+int vpth_render_get_srgb8(vpth_render* r, uint8_t* rgba) {
+  if (!r || !rgba) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto bytes = get_render_srgb8(r->state);
+    memcpy(rgba, bytes.data(), bytes.size());
+  });
+}
+
 int vpth_render_stats(const vpth_render* r, vpt_trace_stats* stats) {
   if (!r || !stats) return VPT_ERR_INVALID;
   return guarded([&] { *stats = get_trace_stats(r->state); });

@@ -351,6 +351,15 @@ void sync_state(pathtrace_state& state) {
   dev.dirty = false;
 }
 
+std::vector<uint8_t> get_render_srgb8(pathtrace_state& state) {
+  auto dstate = device_handle(state);
+  if (!dstate) throw std::invalid_argument("nothing rendered yet");
+  auto bytes = std::vector<uint8_t>((size_t)state.width * state.height * 4);
+  if (vpt_cuda_download_srgb8(dstate, state.samples, bytes.data(), bytes.size()) != VPT_OK)
+    throw std::runtime_error(vpt_cuda_last_error());
+  return bytes;
+}
+
 color_image get_render(const pathtrace_state& state) {
   auto image   = color_image{};
   image.width  = state.width, image.height = state.height, image.linear = true;

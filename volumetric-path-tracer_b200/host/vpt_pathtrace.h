@@ -118,6 +118,9 @@ void sync_state(pathtrace_state& state);
 // Get resulting render (divides by state.samples, yocto_pathtrace.cpp:1105-1116);
 // the second form throws std::invalid_argument on a size / linearity mismatch.
 color_image get_render(const pathtrace_state& state);
+// Output stage on the device: get_render + rgb_to_srgb + float_to_byte (what save_image encodes
+// for 8-bit formats, yocto_sceneio.cpp:523-529); width*height*4 bytes, RGBA.
+std::vector<uint8_t> get_render_srgb8(pathtrace_state& state);
 void        get_render(color_image& render, const pathtrace_state& state);
 
 // The C-ABI scene description (include/vpt_cuda.h) of a host scene; the
