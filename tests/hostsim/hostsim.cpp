@@ -10,10 +10,11 @@
 //
 // usage: hostsim <scene.vptscene> <out.vptarch> [--shader NAME] [--samples N]
 //        [--resolution R] [--bounces B] [--noimplicitmis] [--stmaxiter M]
-//        [--rays rays.vptarch] [--instance K] [--threads T]
+//        [--rays rays.vptarch] [--instance K] [--threads T] [--cull-check]
 #define VPT_HOST_POOL 1
 #define VPT_STACK_CHECK 1
 #define VPT_WORK_COUNTERS 1
+#define VPT_CULL_CHECK 1
 #include <chrono>
 #include <cmath>
 #include <cstring>
@@ -29,7 +30,7 @@ using namespace vpt;
 template <int S>
 static void render_rows(const DScene& sc, const DParams& prm, pathtrace_state& state, int nsamples,
     int tid, int nthreads) {
-  int  stack_mem[vpt_stack_depth];
+  int  stack_mem[vpt_stack_depth * vpt_stack_words];
   auto st = stack_t{stack_mem, 1};
   for (int idx = tid; idx < state.width * state.height; idx += nthreads) {
     auto rng = rng_t{state.rngs[idx].state, state.rngs[idx].inc};
@@ -142,6 +143,7 @@ int main(int argc, const char** argv) {
     else if (a == "--rays") rays_file = next();
     else if (a == "--instance") instance = std::stoi(next());
     else if (a == "--threads") nthreads = std::stoi(next());
+    else if (a == "--cull-check") vpt_cull_check_on = true;
   }
   auto error = std::string{};
   auto scene = scene_data{};
@@ -169,7 +171,7 @@ int main(int argc, const char** argv) {
     auto fl   = std::vector<float>(n * 3);
     auto sid  = std::vector<int>(n * 3);
     auto sfl  = std::vector<float>(n * 4);
-    int  stack_mem[vpt_stack_depth];
+    int  stack_mem[vpt_stack_depth * vpt_stack_words];
     auto st      = stack_t{stack_mem, 1};
     auto has_sdf = sc.num_sdfs + sc.num_vol_instances > 0;
     for (size_t i = 0; i < n; i++) {
@@ -241,8 +243,12 @@ int main(int argc, const char** argv) {
         per_path[i] = (float)(v[i] / paths);
         printf(" %s=%.3f", names[i], per_path[i]);
       }
-      printf(" iq_box_tests=%.3f iq_tri_tests=%.3f\n", g_work.iq_box_tests / paths,
-          g_work.iq_tri_tests / paths);
+      printf(" iq_box_tests=%.3f iq_tri_tests=%.3f node_visits=%.3f cull_tests=%.3f\n",
+          g_work.iq_box_tests / paths, g_work.iq_tri_tests / paths, g_work.node_visits / paths,
+          g_work.cull_tests / paths);
+      if (vpt_cull_check_on)
+        printf("hostsim: cull check: %lld instances culled, %lld of them hold a hit the reference "
+               "would find\n", (long long)g_work.culled, (long long)g_work.cull_wrong);
       out.add_f32("work_per_path", {12}, per_path);
     }
     printf("hostsim: %dx%d %d spp shader=%s %.3f s\n", state.width, state.height, params.samples,

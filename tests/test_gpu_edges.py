@@ -64,12 +64,11 @@ def test_point_and_line_primitives_are_rejected(vpt, tmp_path):
     a["shape3.unsupported"] = np.asarray([5, 0], np.int32)  # five point primitives
     p = str(tmp_path / "points.vptscene")
     vpt.archive.save(p, a)
-    sc = vpt.binding.Scene(p)
     with pytest.raises(vpt.binding.VptError) as e:
+        sc = vpt.binding.Scene(p)
         r = vpt.binding.Render(sc, vpt.binding.make_params(shader="color", samples=1, resolution=32))
         r.trace(1)
     assert "-2" in str(e.value) and "not supported" in str(e.value)
-    sc.close()
 
 
 def test_scene_without_instances_renders_the_environment(vpt, tmp_path):

@@ -2,8 +2,6 @@
 //
 // Reproduces the reference's visit order and arithmetic so that first hits
 // are bit-identical (yocto_bvh.cpp:699-881, yocto_geometry.h:786-868):
-//   * a node's box is tested when it is popped, against the current tmax,
-//     with the slab test's `t1 *= 1.00000024f` and ternary min/max;
 //   * children are visited near-first by the sign of 1/d on the split axis
 //     (the second-pushed child is popped first);
 //   * leaf primitives are tested in stored order and `t <= tmax` accepts, so
@@ -11,13 +9,37 @@
 //   * instance rays are transformed by the host-precomputed non-rigid inverse
 //     frame and their direction is NOT renormalised (t is shared across spaces).
 //
-// Both levels run in ONE loop over ONE stack ("while-while" form): every lane
-// first pops entries until it holds a leaf, then the warp processes leaves
-// together. Stack entries are node indices (>= 0), instance entries (~instance,
-// pushed in reverse so they pop in leaf order) and a sentinel that restores the
-// world-space ray when an instance's subtree is exhausted. Per lane the visit
-// order is exactly the nested two-level walk's; only the SIMT schedule differs
-// (ncu r01: the nested form ran 2.8 of 32 lanes, leaf tests 1.2 of 32).
+// Box tests. The reference tests a node's box when the node is POPPED, against
+// the tmax of that moment: pass_pop = t0 <= min(hi, tmax_pop) * k, with
+// t0 = max(lo, tmin), lo / hi the slab entry / exit and k = 1.00000024f. Here both
+// children of a node are tested when the PARENT is expanded (one 64-byte record
+// holds the two child boxes), failing children are never pushed, and a passing
+// child is pushed with its t0. Because tmax only shrinks and float multiplication
+// by k is monotone,
+//     pass_pop  ==  pass_push  &&  t0 <= tmax_pop * k
+// (if hi < tmax_pop both tests clamp to hi and agree; else the pop test IS
+// t0 <= tmax_pop * k; a NaN t0 fails both, a NaN hi clamps to tmax in both), so
+// the pop-time re-check is one multiply and one compare and the set and order of
+// visited leaves are exactly the reference's. Root boxes (scene, instance) are
+// tested explicitly when they are entered, as the reference does.
+//
+// Instances. The reference has no per-instance box test: every instance of a
+// visited scene leaf gets its ray transformed (3 IEEE divisions for 1/d) and its
+// root box tested in object space. Here a scene leaf first tests the ray against
+// the instance's WORLD box, enlarged by 1e-4 of (extent + |coordinates|) — three
+// orders of magnitude above the float error of either space — and skips the
+// instance if it misses: such a ray passes no primitive of the instance at less
+// than that margin, so the reference finds nothing there either (checked on every
+// culled instance by tests/hostsim --cull-check). Rays with a zero direction
+// component or an origin farther than 100x the box scale are never culled.
+//
+// Both levels run in ONE loop over ONE stack ("while-while" form). Per round a
+// lane pops entries until it holds a leaf or an instance to enter, then the warp
+// enters instances together and tests leaves together (ncu r01: with the instance
+// entry inside the pop loop it ran 5.5 of 32 lanes, leaf tests 4.5 of 32).
+// Stack entries are (ref, t0): ref >= 0 is a child-pair record, ref < 0 carries
+// ~((payload << 2) | tag) with tag 0 = leaf {first primitive record << 3 | count},
+// 1 = instance, 2 = sentinel that restores the world-space ray.
 // Loops are single-exit on purpose: multi-exit forms of this loop hung on
 // sm_100a ("single-exit loops").
 #pragma once
@@ -35,14 +57,18 @@ inline int vpt_stack_high_water = -1;  // tests/hostsim only
 struct stack_t {
   int* base;
   int  stride;
-  VPT_FN int  get(int i) const { return base[i * stride]; }
-  VPT_FN void set(int i, int v) const {
+  // entry i = two words: the ref at row 2 i, its t0 at row 2 i + 1
+  VPT_FN int   ref(int i) const { return base[2 * i * stride]; }
+  VPT_FN float t0(int i) const { return i2f(base[(2 * i + 1) * stride]); }
+  VPT_FN void  push(int i, int r, float t) const {
 #if defined(VPT_STACK_CHECK)
     if (i > vpt_stack_high_water) vpt_stack_high_water = i;
 #endif
-    base[i * stride] = v;
+    base[2 * i * stride]       = r;
+    base[(2 * i + 1) * stride] = f2i(t);
   }
 };
+constexpr int vpt_stack_words = 2;  // ints per entry (sizes the shared-memory columns)
 
 constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
 
@@ -51,7 +77,10 @@ constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
 // which cannot change `t0 <= t1` because t0 >= tmin > 0: the device takes the 1-instruction
 // FMNMX form (12 instead of 24 instructions for the selects). Rays with a zero direction
 // component keep the ternaries, whose NaN behaviour the reference depends on.
-VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1, bool plain) {
+// `t0` (entry distance, independent of tmax) feeds the pop-time re-check.
+constexpr float box_slack = 1.00000024f;
+VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1, bool plain,
+    float& t0) {
   VPT_WORK(box_tests, 1);
   auto bmin   = f3{n0.x, n0.y, n0.z};
   auto bmax   = f3{n0.w, n1.x, n1.y};
@@ -59,20 +88,33 @@ VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1, b
   auto it_max = (bmax - o) * dinv;
 #if defined(__CUDA_ARCH__)
   if (plain) {
-    auto t0 = fmaxf(fmaxf(fmaxf(fminf(it_min.x, it_max.x), fminf(it_min.y, it_max.y)),
-                        fminf(it_min.z, it_max.z)), tmin);
+    t0 = fmaxf(fmaxf(fmaxf(fminf(it_min.x, it_max.x), fminf(it_min.y, it_max.y)),
+                   fminf(it_min.z, it_max.z)), tmin);
     auto t1 = fminf(fminf(fminf(fmaxf(it_min.x, it_max.x), fmaxf(it_min.y, it_max.y)),
                         fmaxf(it_min.z, it_max.z)), tmax);
-    t1 *= 1.00000024f;
+    t1 *= box_slack;
     return t0 <= t1;
   }
 #endif
   auto lo = vmin(it_min, it_max);
   auto hi = vmax(it_min, it_max);
-  auto t0 = vmax(max3(lo), tmin);
+  t0      = vmax(max3(lo), tmin);
   auto t1 = vmin(min3(hi), tmax);
-  t1 *= 1.00000024f;
+  t1 *= box_slack;
   return t0 <= t1;
+}
+
+// Conservative world-space test of an instance's enlarged box (see the header). Only for
+// `plain` rays; a NaN anywhere reports a hit.
+VPT_FN bool misses_instance_box(f3 o, f3 dinv, float tmin, float tmax, f4 b0, f4 b1) {
+  VPT_WORK(cull_tests, 1);
+  auto it_min = (f3{b0.x, b0.y, b0.z} - o) * dinv;
+  auto it_max = (f3{b0.w, b1.x, b1.y} - o) * dinv;
+  auto t0 = fmaxf(fmaxf(fmaxf(fminf(it_min.x, it_max.x), fminf(it_min.y, it_max.y)),
+                      fminf(it_min.z, it_max.z)), tmin);
+  auto t1 = fminf(fminf(fminf(fmaxf(it_min.x, it_max.x), fmaxf(it_min.y, it_max.y)),
+                      fmaxf(it_min.z, it_max.z)), tmax);
+  return t0 > t1 * 1.001f;
 }
 VPT_FN bool all_finite(f3 v) { return vfinite(v.x) && vfinite(v.y) && vfinite(v.z); }
 
@@ -115,7 +157,15 @@ VPT_FN bool intersect_quad(f3 o, f3 d, float tmin, float tmax, f3 p0, f3 p1, f3 
   return hit;
 }
 
-constexpr int stack_sentinel = (int)0x80000000;
+#if defined(VPT_CULL_CHECK)
+// tests/hostsim --cull-check: walks every culled instance as the reference would
+inline bool vpt_cull_check_on = false;
+inline void vpt_cull_check(const DScene& sc, int instance, const ray3& ray, float tmax);
+#endif
+
+constexpr int ref_leaf = 0, ref_instance = 1, ref_sentinel = 2;
+VPT_FN constexpr int make_ref(int payload, int tag) { return ~((payload << 2) | tag); }
+constexpr int leaf_start_limit = 1 << 26;  // f4 index of a leaf's first primitive record
 #if !defined(VPT_TRAV_POPS)
 #define VPT_TRAV_POPS 8
 #endif
@@ -128,100 +178,138 @@ struct trav_t {
   f3    wdinv;       // 1 / d of the world-space ray, kept so leaving an instance costs no divisions
   float tmin, tmax;
   bool  plain, wplain;  // all of dinv finite (see intersect_box), for the current / world ray
+  bool  cull;           // world-space instance culling allowed for this ray
+  float omax;           // largest |coordinate| of the world-space origin
   int   kind;        // -1: scene level, else the element kind of the entered shape
   int   inst, cur;
   hit_t h;
 
-  // `first`: a scene node index, or ~instance for the instance-targeted query
-  VPT_FN void begin(int first, const ray3& ray, stack_t st) {
+  // `first`: < 0 for the whole scene, else the instance of the instance-targeted query
+  VPT_FN void begin(const DScene& sc, int first, const ray3& ray, stack_t st) {
     h = hit_t{-1, -1, {0, 0}, 0, false};
     o = ray.o, d = ray.d;
     tmin = ray.tmin, tmax = ray.tmax;
     dinv  = f3{1 / d.x, 1 / d.y, 1 / d.z};
     plain = all_finite(dinv);
     wdinv = dinv, wplain = plain;
+    omax  = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+    cull  = plain && vfinite(omax);
     kind = -1, inst = -1, cur = 0;
-    st.set(cur++, first);
+    if (first >= 0) {
+      st.push(cur++, make_ref(first, ref_instance), 0);
+    } else if (sc.num_instances > 0) {
+      float t0;
+      if (intersect_box(o, dinv, tmin, tmax, sc.scene_box0, sc.scene_box1, plain, t0))
+        st.push(cur++, sc.scene_root, t0);
+    }
   }
   VPT_FN bool done() const { return cur == 0; }
 
-  // One round: pop until this lane holds a leaf, its stack is empty or it has popped
-  // `trav_pops` entries, then process the leaf if it has one. The bound keeps lanes that
-  // already hold a leaf from waiting on the lane with the longest descent (pops between
-  // leaves average ~10 and are roughly geometric, so the maximum over a warp was ~22 per
-  // round in ncu r01 while the mean lane needed 10); it changes the SIMT schedule only.
+  // One round: pop until this lane holds a leaf or an instance to enter, its stack is empty
+  // or it has popped `trav_pops` entries; then enter the instance / process the leaf. The
+  // bound keeps lanes that already hold work from waiting on the lane with the longest
+  // descent; it changes the SIMT schedule only.
   VPT_FN void round(const DScene& sc, const ray3& ray, stack_t st) {
-    int lstart = 0, lnum = 0;
+    int leaf = 0, enter = -1;
     int pops = trav_pops;
-    while (cur != 0 && lnum == 0 && pops != 0) {
+    while (cur != 0 && leaf == 0 && enter < 0 && pops != 0) {
       pops--;
-      int e = st.get(--cur);
+      int   e  = st.ref(--cur);
+      float te = st.t0(cur);
       if (e >= 0) {
-        auto n0 = ld4(sc.nodes + 2 * e), n1 = ld4(sc.nodes + 2 * e + 1);
-        if (intersect_box(o, dinv, tmin, tmax, n0, n1, plain)) {
-          auto start = f2i(n1.z), meta = f2i(n1.w);
-          if (meta >> 24) {
-            auto axis = (meta >> 16) & 3;
-            auto sgn  = (axis == 0 ? dinv.x : (axis == 1 ? dinv.y : dinv.z)) < 0;
-            // reference order: push (c0, c1) if the sign is set, else (c1, c0);
-            // the last pushed child is visited first
-            st.set(cur++, sgn ? start : start + 1);
-            st.set(cur++, sgn ? start + 1 : start);
-          } else {
-            lstart = start, lnum = meta & 0xffff;
-          }
+        if (te <= tmax * box_slack) {
+          VPT_WORK(node_visits, 1);
+          auto p  = sc.nodes + 4 * (size_t)e;
+          auto a0 = ld4(p), a1 = ld4(p + 1), b0 = ld4(p + 2), b1 = ld4(p + 3);
+          float ta, tb;
+          bool  pa = intersect_box(o, dinv, tmin, tmax, a0, a1, plain, ta);
+          bool  pb = intersect_box(o, dinv, tmin, tmax, b0, b1, plain, tb);
+          auto  axis = f2i(a1.w);
+          auto  sgn  = (axis == 0 ? dinv.x : (axis == 1 ? dinv.y : dinv.z)) < 0;
+          // reference order: push (c0, c1) if the sign is set, else (c1, c0);
+          // the last pushed child is visited first
+          int   r1 = f2i(sgn ? a1.z : b1.z), r2 = f2i(sgn ? b1.z : a1.z);
+          float t1 = sgn ? ta : tb, t2 = sgn ? tb : ta;
+          bool  p1 = sgn ? pa : pb, p2 = sgn ? pb : pa;
+          if (p1) st.push(cur++, r1, t1);
+          if (p2) st.push(cur++, r2, t2);
         }
-      } else if (e == stack_sentinel) {
-        o = ray.o, d = ray.d;
-        dinv = wdinv, plain = wplain;
-        kind = -1;
       } else {
-        inst = ~e;
-        VPT_WORK(inst_transforms, 1);
-        auto t  = sc.inst_trav + 4 * inst;
-        auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
+        int x = ~e, tag = x & 3;
+        if (tag == ref_leaf) {
+          if (te <= tmax * box_slack) leaf = x >> 2;
+        } else if (tag == ref_instance) {
+          enter = x >> 2;
+        } else {
+          o = ray.o, d = ray.d;
+          dinv = wdinv, plain = wplain;
+          kind = -1;
+        }
+      }
+    }
+    if (enter >= 0) {
+      // transform the ray, test the shape's root box (yocto_bvh.cpp:854-858, :714-722)
+      VPT_WORK(inst_transforms, 1);
+      auto t  = sc.inst_trav + 4 * enter;
+      auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
+      if (f2i(c0.w) >= 0) {
         auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
-        auto root = f2i(c0.w);
-        if (root >= 0) {
-          o     = transform_point(inv, ray.o);
-          d     = transform_vector(inv, ray.d);
-          dinv  = f3{1 / d.x, 1 / d.y, 1 / d.z};
-          plain = all_finite(dinv);
-          kind  = f2i(c1.w);
-          st.set(cur++, stack_sentinel);
-          st.set(cur++, root);
+        auto r0 = ld4(sc.inst_root + 2 * enter), r1 = ld4(sc.inst_root + 2 * enter + 1);
+        auto lo = transform_point(inv, ray.o);
+        auto ld = transform_vector(inv, ray.d);
+        auto li = f3{1 / ld.x, 1 / ld.y, 1 / ld.z};
+        auto lp = all_finite(li);
+        float t0;
+        if (intersect_box(lo, li, tmin, tmax, r0, r1, lp, t0)) {
+          o = lo, d = ld, dinv = li, plain = lp;
+          inst = enter;
+          kind = f2i(c1.w);
+          st.push(cur++, make_ref(0, ref_sentinel), 0);
+          st.push(cur++, f2i(r1.z), t0);
         }
       }
     }
     // leaves: primitives in stored order; a scene leaf queues its instances
-    if (kind == kind_quads) {
-      for (auto i = 0; i < lnum; i++) {
-        auto p = sc.prims + lstart + 4 * i;
-        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), q = ld4(p + 3);
-        if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(q), h.uv, h.distance)) {
-          h.hit = true, h.instance = inst, h.element = f2i(a.w);
-          tmax = h.distance;
+    if (leaf != 0) {
+      int lstart = leaf >> 3, lnum = leaf & 7;
+      if (kind == kind_quads) {
+        for (auto i = 0; i < lnum; i++) {
+          auto p = sc.prims + lstart + 4 * i;
+          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), q = ld4(p + 3);
+          if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(q), h.uv, h.distance)) {
+            h.hit = true, h.instance = inst, h.element = f2i(a.w);
+            tmax = h.distance;
+          }
+        }
+      } else if (kind >= 0) {
+        for (auto i = 0; i < lnum; i++) {
+          auto p = sc.prims + lstart + 3 * i;
+          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
+          if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), h.uv, h.distance)) {
+            h.hit = true, h.instance = inst, h.element = f2i(a.w);
+            tmax = h.distance;
+          }
+        }
+      } else {
+        // reverse order, so that the instances pop in leaf order
+        for (auto i = lnum - 1; i >= 0; i--) {
+          auto p  = sc.scene_leaves + 2 * (lstart + i);
+          auto b0 = ld4(p), b1 = ld4(p + 1);
+          bool skip = cull && omax <= b1.w && misses_instance_box(o, dinv, tmin, tmax, b0, b1);
+#if defined(VPT_CULL_CHECK)
+          if (skip && vpt_cull_check_on) vpt_cull_check(sc, f2i(b1.z), ray, tmax);
+#endif
+          if (!skip) st.push(cur++, make_ref(f2i(b1.z), ref_instance), 0);
         }
       }
-    } else if (kind >= 0) {
-      for (auto i = 0; i < lnum; i++) {
-        auto p = sc.prims + lstart + 3 * i;
-        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
-        if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), h.uv, h.distance)) {
-          h.hit = true, h.instance = inst, h.element = f2i(a.w);
-          tmax = h.distance;
-        }
-      }
-    } else {
-      for (auto i = lnum - 1; i >= 0; i--) st.set(cur++, ~ld1(sc.scene_prims + lstart + i));
     }
   }
 };
 
-// Closest hit below `first`. Uses stack slots [0, ...).
+// Closest hit of the scene (`first` < 0) or of one instance. Uses stack slots [0, ...).
 VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) {
   trav_t t;
-  t.begin(first, ray, st);
+  t.begin(sc, first, ray, st);
   VPT_GUARD_DECL(guard);
   while (!t.done()) {
     VPT_GUARD_STEP(2, guard, 30000);
@@ -230,6 +318,16 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
   return t.h;
 }
 
+#if defined(VPT_CULL_CHECK)
+inline void vpt_cull_check(const DScene& sc, int instance, const ray3& ray, float tmax) {
+  int  mem[vpt_stack_depth * vpt_stack_words];
+  auto r = ray;
+  r.tmax = tmax;
+  VPT_WORK(culled, 1);
+  if (traverse(sc, instance, r, stack_t{mem, 1}).hit) VPT_WORK(cull_wrong, 1);
+}
+#endif
+
 // Instance-targeted query (yocto_bvh.cpp:874-881), used by the light pdf.
 VPT_FN hit_t intersect_instance(const DScene& sc, int instance, const ray3& ray, stack_t st) {
   VPT_WORK(instance_queries, 1);
@@ -237,7 +335,7 @@ VPT_FN hit_t intersect_instance(const DScene& sc, int instance, const ray3& ray,
   // share of the box / primitive tests spent in light-pdf queries (run hostsim with --threads 1)
   long long b0 = g_work.box_tests, t0 = g_work.tri_tests;
 #endif
-  auto h     = traverse(sc, ~instance, ray, st);
+  auto h     = traverse(sc, instance, ray, st);
   h.instance = instance;
 #if defined(VPT_WORK_COUNTERS) && !defined(__CUDACC__)
   g_work.iq_box_tests += g_work.box_tests - b0, g_work.iq_tri_tests += g_work.tri_tests - t0;
@@ -248,8 +346,7 @@ VPT_FN hit_t intersect_instance(const DScene& sc, int instance, const ray3& ray,
 // Closest hit over the whole scene (yocto_bvh.cpp:800-871).
 VPT_FN hit_t intersect_scene(const DScene& sc, const ray3& ray, stack_t st) {
   VPT_WORK(scene_queries, 1);
-  if (sc.scene_root < 0) return hit_t{-1, -1, {0, 0}, 0, false};
-  return traverse(sc, sc.scene_root, ray, st);
+  return traverse(sc, -1, ray, st);
 }
 
 }  // namespace vpt

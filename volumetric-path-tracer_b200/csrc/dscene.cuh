@@ -2,16 +2,24 @@
 //
 // Everything a path touches is a 16-byte-aligned record read with 128-bit
 // loads through the read-only path:
-//   nodes      2 x f4 per BVH node: {min.xyz, max.x} {max.y, max.z, start, meta}
-//              meta = num | axis << 16 | internal << 24. All shape BVHs and the
-//              scene BVH are concatenated; `start` is rebased at upload so an
-//              internal node points at its first child in this array and a
-//              leaf at its first primitive record (f4 index) / scene_prims slot.
+//   nodes      4 x f4 (64 bytes) per INTERNAL BVH node = the boxes of its two
+//              children: {c0.min.xyz, c0.max.x} {c0.max.yz, ref0, axis}
+//              {c1.min.xyz, c1.max.x} {c1.max.yz, ref1, 0}. A ref >= 0 is the
+//              record of an internal child; a leaf child has no record, its ref
+//              is ~((first primitive record (f4 index) << 3 | count) << 2)
+//              (scene BVH: first slot of scene_leaves). `axis` is the split axis
+//              of the node the record belongs to. All shape BVHs and the scene
+//              BVH are concatenated. One 64-byte fetch per visited node.
 //   prims      primitives gathered in BVH leaf order, vertex positions inline:
 //              quad = 4 x f4 {p_k.xyz, payload}, triangle = 3 x f4;
 //              payload of the first f4 = element index.
+//   scene_leaves 2 x f4 per scene-BVH primitive slot: the instance's world box
+//              enlarged for culling {min.xyz, max.x} {max.yz, instance id,
+//              largest |ray origin| culling is valid for (-1: never cull)}
 //   inst_trav  4 x f4 per instance: columns of inverse(frame, non_rigid) in xyz;
-//              w = {shape root node, shape kind, shape id, material id}
+//              w = {0 or -1 (no geometry), shape kind, shape id, material id}
+//   inst_root  2 x f4 per instance: the shape BVH's root box and ref
+//              {min.xyz, max.x} {max.yz, ref, 0}
 //   inst_frame 4 x f4 per instance: forward frame columns.
 // The reference layout this replaces: bvh_data / shape_data / instance_data
 // (yocto_bvh.h:73-92, yocto_shape.h:74, yocto_scene.h:142-148).
@@ -27,10 +35,12 @@ struct DScene {
   // acceleration
   const f4*  nodes;
   const f4*  prims;
-  const int* scene_prims;
+  const f4*  scene_leaves;
   const f4*  inst_trav;
+  const f4*  inst_root;
   const f4*  inst_frame;
-  int        scene_root;  // node index of the scene BVH root, -1 if none
+  f4         scene_box0, scene_box1;  // root box of the scene BVH {min.xyz, max.x} {max.yz, 0, 0}
+  int        scene_root;              // ref of the scene BVH root (valid if num_instances > 0)
   int        num_instances;
   // shapes for shading: 2 x i4 per shape {kind, pos, nrm, tex} {col, elem, 0, 0}
   const i4*    shapes;

@@ -111,19 +111,64 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
 
   std::vector<f4>  nodes, prims, inst_trav, inst_frame, vcol, materials, cameras, environments;
   std::vector<f4>  vol_instances, volumes, sdfs, texf;
-  std::vector<int> scene_prims;
+  std::vector<f4>  scene_leaves, inst_root;
   std::vector<i4>  shapes, elems, textures, lights;
   std::vector<float>         vpos, vnrm, vtex, cdf, voxels, srgb_lut(256);
   std::vector<unsigned char> texb;
 
-  auto push_node = [&](const vpt_bvh_node& n, int start) {
-    nodes.push_back({n.bbox_min[0], n.bbox_min[1], n.bbox_min[2], n.bbox_max[0]});
-    int meta = ((int)n.num & 0xffff) | (((int)n.axis & 0xff) << 16) | ((n.internal ? 1 : 0) << 24);
-    nodes.push_back({n.bbox_max[1], n.bbox_max[2], i2f(start), i2f(meta)});
+  // Appends one BVH in the child-pair layout of dscene.cuh. `leaf_base` / `leaf_stride`
+  // rebase a leaf's `start` (f4 index of its first primitive record, or its first
+  // scene_leaves slot). Returns the root's {box, ref} through root0 / root1.
+  auto push_bvh = [&](const vpt_bvh_desc& bvh, int leaf_base, int leaf_stride, f4& root0,
+                      f4& root1, std::string& why) -> bool {
+    int              pair_base = (int)(nodes.size() / 4);
+    std::vector<int> pair_of(bvh.num_nodes, -1);
+    int              npairs = 0;
+    for (int n = 0; n < bvh.num_nodes; n++)
+      if (bvh.nodes[n].internal) pair_of[n] = npairs++;
+    auto ref_of = [&](int n, int& ref) -> bool {
+      auto& node = bvh.nodes[n];
+      if (node.internal) {
+        ref = pair_base + pair_of[n];
+        return true;
+      }
+      long long start = (long long)leaf_base + (long long)node.start * leaf_stride;
+      if (node.num < 1 || node.num > 7 || start >= leaf_start_limit) {
+        why = "bvh leaf with " + std::to_string(node.num) + " primitives at record " +
+              std::to_string(start) + " does not fit the device leaf reference";
+        return false;
+      }
+      ref = make_ref(((int)start << 3) | (int)node.num, ref_leaf);
+      return true;
+    };
+    auto box0 = [](const vpt_bvh_node& n) {
+      return f4{n.bbox_min[0], n.bbox_min[1], n.bbox_min[2], n.bbox_max[0]};
+    };
+    for (int n = 0; n < bvh.num_nodes; n++) {
+      auto& node = bvh.nodes[n];
+      if (!node.internal) continue;
+      if (node.start < 1 || node.start + 1 >= bvh.num_nodes) {
+        why = "bvh child link out of range";
+        return false;
+      }
+      auto &c0 = bvh.nodes[node.start], &c1 = bvh.nodes[node.start + 1];
+      int  r0 = 0, r1 = 0;
+      if (!ref_of(node.start, r0) || !ref_of(node.start + 1, r1)) return false;
+      nodes.push_back(box0(c0));
+      nodes.push_back({c0.bbox_max[1], c0.bbox_max[2], i2f(r0), i2f((int)node.axis & 3)});
+      nodes.push_back(box0(c1));
+      nodes.push_back({c1.bbox_max[1], c1.bbox_max[2], i2f(r1), i2f(0)});
+    }
+    int rr = 0;
+    if (!ref_of(0, rr)) return false;
+    root0 = box0(bvh.nodes[0]);
+    root1 = {bvh.nodes[0].bbox_max[1], bvh.nodes[0].bbox_max[2], i2f(rr), i2f(0)};
+    return true;
   };
 
   // ---- shapes: vertex pools, element indices, leaf-ordered primitive records ----
-  std::vector<int> shape_root(in.num_shapes, -1), shape_kind(in.num_shapes, kind_empty);
+  std::vector<int> shape_kind(in.num_shapes, kind_empty);
+  std::vector<f4>  shape_root0(in.num_shapes, f4{0, 0, 0, 0}), shape_root1(in.num_shapes, f4{0, 0, 0, 0});
   int              max_shape_depth = 0;
   for (int s = 0; s < in.num_shapes; s++) {
     auto& sh = in.shapes[s];
@@ -174,9 +219,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     if (depth < 0) return fail(VPT_ERR_INVALID, "malformed shape bvh " + std::to_string(s));
     max_shape_depth = depth > max_shape_depth ? depth : max_shape_depth;
     int stride    = kind == kind_triangles ? 3 : 4;
-    int node_base = (int)(nodes.size() / 2);
     int prim_base = (int)prims.size();
-    shape_root[s] = node_base;
     for (int k = 0; k < bvh.num_primitives; k++) {
       int e = bvh.primitives[k];
       if (e < 0 || e >= nelem)
@@ -190,14 +233,12 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     }
     for (int n = 0; n < bvh.num_nodes; n++) {
       auto& node = bvh.nodes[n];
-      if (node.internal) {
-        push_node(node, node_base + node.start);
-      } else {
-        if (node.start < 0 || node.start + node.num > bvh.num_primitives)
-          return fail(VPT_ERR_INVALID, "bvh leaf out of range in shape " + std::to_string(s));
-        push_node(node, prim_base + node.start * stride);
-      }
+      if (!node.internal && (node.start < 0 || node.start + node.num > bvh.num_primitives))
+        return fail(VPT_ERR_INVALID, "bvh leaf out of range in shape " + std::to_string(s));
     }
+    auto why = std::string{};
+    if (!push_bvh(bvh, prim_base, stride, shape_root0[s], shape_root1[s], why))
+      return fail(VPT_ERR_UNSUPPORTED, why + " (shape " + std::to_string(s) + ")");
   }
 
   // ---- instances + scene bvh ----------------------------------------------------
@@ -208,27 +249,63 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
       return fail(VPT_ERR_INVALID, "instance " + std::to_string(i) + " references a missing shape/material");
     auto frame = to_frame(inst.frame);
     auto inv   = inverse_frame(frame, true);  // yocto_bvh.cpp:854-855
-    inst_trav.push_back(pack(inv.x, shape_root[inst.shape]));
+    inst_trav.push_back(pack(inv.x, shape_kind[inst.shape] == kind_empty ? -1 : 0));
     inst_trav.push_back(pack(inv.y, shape_kind[inst.shape]));
     inst_trav.push_back(pack(inv.z, inst.shape));
     inst_trav.push_back(pack(inv.o, inst.material));
+    inst_root.push_back(shape_root0[inst.shape]);
+    inst_root.push_back(shape_root1[inst.shape]);
     inst_frame.push_back(pack(frame.x, inst.shape));
     inst_frame.push_back(pack(frame.y, inst.material));
     inst_frame.push_back(pack(frame.z, 0));
     inst_frame.push_back(pack(frame.o, 0));
   }
-  int scene_root = -1, scene_depth = 0, scene_leaf = 0;
+  // world box of an instance for culling (bvh.cuh): the 8 transformed corners of the shape's
+  // root box, enlarged by 1e-4 of (extent + |coordinates|); valid for ray origins up to 100x
+  // that scale. Anything non-finite or empty disables culling for the instance.
+  auto cull_record = [&](int i, f4& b0, f4& b1) {
+    auto& inst = in.instances[i];
+    b0 = {0, 0, 0, 0}, b1 = {0, 0, i2f(i), -1.0f};
+    if (shape_kind[inst.shape] == kind_empty) return;
+    auto   r0 = shape_root0[inst.shape], r1 = shape_root1[inst.shape];
+    double lo[3] = {r0.x, r0.y, r0.z}, hi[3] = {r0.w, r1.x, r1.y};
+    double wmin[3] = {1e300, 1e300, 1e300}, wmax[3] = {-1e300, -1e300, -1e300};
+    for (int c = 0; c < 8; c++) {
+      double p[3] = {c & 1 ? hi[0] : lo[0], c & 2 ? hi[1] : lo[1], c & 4 ? hi[2] : lo[2]};
+      for (int k = 0; k < 3; k++) {
+        double w = (double)inst.frame[0 + k] * p[0] + (double)inst.frame[3 + k] * p[1] +
+                   (double)inst.frame[6 + k] * p[2] + (double)inst.frame[9 + k];
+        if (!(w >= -1e30 && w <= 1e30)) return;  // NaN / overflow: never cull
+        wmin[k] = w < wmin[k] ? w : wmin[k];
+        wmax[k] = w > wmax[k] ? w : wmax[k];
+      }
+    }
+    double scale = 0;
+    for (int k = 0; k < 3; k++) {
+      double m = std::fabs(wmin[k]) > std::fabs(wmax[k]) ? std::fabs(wmin[k]) : std::fabs(wmax[k]);
+      double s = (wmax[k] - wmin[k]) + m;
+      scale    = s > scale ? s : scale;
+    }
+    if (!(scale > 0)) return;
+    double margin = 1e-4 * scale;
+    b0 = {(float)(wmin[0] - margin), (float)(wmin[1] - margin), (float)(wmin[2] - margin),
+        (float)(wmax[0] + margin)};
+    b1 = {(float)(wmax[1] + margin), (float)(wmax[2] + margin), i2f(i), (float)(100 * scale)};
+  };
+  int scene_root = 0, scene_depth = 0, scene_leaf = 0;
+  f4  scene_box0{0, 0, 0, 0}, scene_box1{0, 0, 0, 0};
   if (in.num_instances > 0) {
     auto& bvh = in.scene_bvh;
     if (bvh.num_nodes <= 0 || bvh.num_primitives != in.num_instances)
       return fail(VPT_ERR_INVALID, "scene bvh does not match the instance list");
     scene_depth = bvh_depth(bvh);
     if (scene_depth < 0) return fail(VPT_ERR_INVALID, "malformed scene bvh");
-    scene_root = (int)(nodes.size() / 2);
     for (int k = 0; k < bvh.num_primitives; k++) {
       if (bvh.primitives[k] < 0 || bvh.primitives[k] >= in.num_instances)
         return fail(VPT_ERR_INVALID, "scene bvh primitive out of range");
-      scene_prims.push_back(bvh.primitives[k]);
+      f4 b0, b1;
+      cull_record(bvh.primitives[k], b0, b1);
+      scene_leaves.push_back(b0), scene_leaves.push_back(b1);
     }
     for (int n = 0; n < bvh.num_nodes; n++) {
       auto& node = bvh.nodes[n];
@@ -237,8 +314,13 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
           return fail(VPT_ERR_INVALID, "scene bvh leaf out of range");
         scene_leaf = node.num > scene_leaf ? node.num : scene_leaf;
       }
-      push_node(node, node.internal ? scene_root + node.start : node.start);
     }
+    auto why = std::string{};
+    f4   root1;
+    if (!push_bvh(bvh, 0, 1, scene_box0, root1, why))
+      return fail(VPT_ERR_UNSUPPORTED, why + " (scene bvh)");
+    scene_box1 = {root1.x, root1.y, 0, 0};
+    scene_root = f2i(root1.z);
   }
   // one stack for both levels (bvh.cuh): a sibling per scene level, the queued
   // instances of one scene leaf, the sentinel, then a sibling per shape level
@@ -356,8 +438,9 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   if (e == cudaSuccess) e = p.upload(vec, &d.field)
   VPT_UP(nodes, nodes);
   VPT_UP(prims, prims);
-  VPT_UP(scene_prims, scene_prims);
+  VPT_UP(scene_leaves, scene_leaves);
   VPT_UP(inst_trav, inst_trav);
+  VPT_UP(inst_root, inst_root);
   VPT_UP(inst_frame, inst_frame);
   VPT_UP(shapes, shapes);
   VPT_UP(vpos, vpos);
@@ -385,6 +468,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
         std::string("scene upload failed: ") + cudaGetErrorString(e));
   }
   d.scene_root        = scene_root;
+  d.scene_box0 = scene_box0, d.scene_box1 = scene_box1;
   d.num_instances     = in.num_instances;
   d.num_environments  = in.num_environments;
   d.num_lights        = in.num_lights;

@@ -168,7 +168,7 @@ static cudaError_t launch_mega(const vpt_scene* scene, vpt_state* state, const D
   int    npix   = state->width * state->height;
   int    slots  = tile_slot_count(state->width, state->height);
   int    blocks = (slots + mega_block - 1) / mega_block;
-  size_t smem   = (size_t)scene->flat.stack_depth * mega_block * sizeof(int);
+  size_t smem   = (size_t)scene->flat.stack_depth * vpt_stack_words * mega_block * sizeof(int);
   auto   kernel = k_render_mega<S>;
   if (smem > 48 * 1024) {
     auto e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -469,7 +469,7 @@ int vpt_cuda_intersect(vpt_scene* scene, const float* rays, int n, int instance,
   if (e == cudaSuccess)
     e = cudaMemcpy(d_rays, rays, (size_t)n * 8 * sizeof(float), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) {
-    size_t smem = (size_t)scene->flat.stack_depth * mega_block * sizeof(int);
+    size_t smem = (size_t)scene->flat.stack_depth * vpt_stack_words * mega_block * sizeof(int);
     if (smem > 48 * 1024)
       e = cudaFuncSetAttribute(k_intersect, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) {

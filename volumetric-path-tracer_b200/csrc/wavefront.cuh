@@ -312,8 +312,7 @@ __global__ void __launch_bounds__(wf_block, 7)
         if constexpr (sdf) {
           sp.begin(ray);
         } else {
-          t.begin(sc.scene_root, ray, st);
-          if (sc.scene_root < 0) t.cur = 0;  // no instances: every ray misses
+          t.begin(sc, -1, ray, st);
         }
         has_ray = true;
       }
@@ -561,7 +560,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   auto e = wf.reserve(slots);
   if (e != cudaSuccess) return e;
   auto&  w    = wf.view;
-  size_t smem = (size_t)scene.stack_depth * wf_block * sizeof(int);
+  size_t smem = (size_t)scene.stack_depth * vpt_stack_words * wf_block * sizeof(int);
   if (smem > 48 * 1024) {
     e = cudaFuncSetAttribute(k_wf_extend<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
