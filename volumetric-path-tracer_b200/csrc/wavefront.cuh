@@ -43,7 +43,8 @@
 namespace vpt {
 
 constexpr int wf_block   = 128;
-constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped)
+constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped), last: suspended
+constexpr int wf_class_susp = wf_classes - 1;
 
 struct wf_counters {
   int                count_ext[2];  // extend queue sizes (double buffered)
@@ -52,7 +53,9 @@ struct wf_counters {
   unsigned long long rays_extend, rays_lightpdf, paths_done;
   int                class_count[wf_classes];
   int                ext_head;  // next unclaimed entry of the extend queue (persistent extend)
-  int                pad2[3];
+  int                count_shade;    // entries of the class-sorted queue that k_wf_shade runs
+  int                susp_count[2];  // suspended-ray records in use, per pool
+  unsigned long long rays_resumed;   // queue entries that were continuations, not new rays
 };
 
 // One 160-byte record per slot (5 aligned 32-byte sectors), fields in the order the
@@ -82,11 +85,16 @@ struct wf_view {
   int *       queue_ext[2], *queue_pdf;
   int *       queue_shade, *sort_key;  // class-sorted slots; (class << 24 | rank) per entry
   wf_counters* counters;
+  // suspended traversals (k_wf_extend_persistent): two pools of `susp_f4`-f4 records,
+  // written by the extend launch of one iteration and read by the next one
+  f4* susp[2];
+  int susp_f4;
 };
 
 struct wavefront_buffers {
   bool         live     = false;
   int          capacity = 0;
+  size_t       susp_bytes = 0;
   wf_view      view{};
   wf_counters* host_counters = nullptr;  // pinned
   cudaEvent_t  poll = nullptr, k0 = nullptr, k1 = nullptr;
@@ -95,11 +103,28 @@ struct wavefront_buffers {
     cudaFree(view.rec);
     cudaFree(view.queue_ext[0]);
     cudaFree(view.counters);
+    if (view.susp[0]) cudaFree(view.susp[0]);
     if (host_counters) cudaFreeHost(host_counters);
     if (poll) cudaEventDestroy(poll);
     if (k0) cudaEventDestroy(k0);
     if (k1) cudaEventDestroy(k1);
     *this = wavefront_buffers{};
+  }
+  // `susp_records` suspended-ray records of `susp_f4` f4 each, per pool
+  cudaError_t reserve_suspended(int susp_records, int susp_f4) {
+    size_t bytes = sizeof(f4) * (size_t)susp_f4 * (size_t)susp_records;
+    view.susp_f4 = susp_f4;
+    if (bytes <= susp_bytes) {
+      view.susp[1] = view.susp[0] + (size_t)susp_f4 * susp_records;
+      return cudaSuccess;
+    }
+    if (view.susp[0]) cudaFree(view.susp[0]);
+    view.susp[0] = view.susp[1] = nullptr, susp_bytes = 0;
+    auto e = cudaMalloc(&view.susp[0], 2 * bytes);
+    if (e != cudaSuccess) return e;
+    view.susp[1] = view.susp[0] + (size_t)susp_f4 * susp_records;
+    susp_bytes   = bytes;
+    return cudaSuccess;
   }
   cudaError_t reserve(int slots) {
     if (capacity >= slots) return cudaSuccess;
@@ -126,6 +151,7 @@ struct wavefront_buffers {
 
 // ---- per-slot state <-> registers -------------------------------------------
 constexpr int wf_bit_hit = 1 << 16, wf_bit_vol = 1 << 17, wf_bit_isec = 1 << 18;
+constexpr int wf_bit_susp = 1 << 19;  // the slot's ray is a suspended traversal to be resumed
 
 // `store_vol`: the volume fields only change when a path enters a volume
 template <int S>
@@ -198,6 +224,47 @@ __device__ __forceinline__ bool wf_finish(const DScene& sc, const DParams& prm, 
   return true;
 }
 
+
+// ---- suspended traversals ------------------------------------------------------
+// Once the extend queue is exhausted a persistent warp only drains: its lanes finish one by
+// one and the warp keeps issuing for the few that are left (ncu r01: 16.7 of 32 lanes held a
+// ray). Instead, when at most `wf_suspend` lanes are still walking, the warp parks them: the
+// walk's registers and stack go to a record in HBM, the slot goes to the NEXT iteration's
+// extend queue flagged wf_bit_susp, and that launch resumes the walk where it stopped, packed
+// into full warps with the new rays. The ray's own sequence of operations is unchanged, so
+// hits stay bit-identical; only the iteration in which the slot reaches shade moves.
+// Record: 7 f4 of registers, then the stack entries two per f4.
+constexpr int wf_susp_head = 7;
+inline int wf_susp_record_f4(int stack_depth) { return wf_susp_head + (stack_depth + 1) / 2; }
+
+__device__ __forceinline__ void wf_suspend_ray(f4* rec, const trav_t& t, stack_t st) {
+  int bits = (t.plain ? 1 : 0) | (t.wplain ? 2 : 0) | (t.cull ? 4 : 0) | (t.h.hit ? 8 : 0);
+  rec[0] = {t.o.x, t.o.y, t.o.z, t.d.x};
+  rec[1] = {t.d.y, t.d.z, t.dinv.x, t.dinv.y};
+  rec[2] = {t.dinv.z, t.wdinv.x, t.wdinv.y, t.wdinv.z};
+  rec[3] = {t.tmin, t.tmax, t.omax, i2f(bits)};
+  rec[4] = {i2f(t.kind), i2f(t.inst), i2f(t.cur), i2f(t.h.instance)};
+  rec[5] = {i2f(t.h.element), t.h.uv.x, t.h.uv.y, t.h.distance};
+  for (int i = 0; i < t.cur; i += 2)
+    rec[wf_susp_head + (i >> 1)] = {i2f(st.ref(i)), st.t0(i), i + 1 < t.cur ? i2f(st.ref(i + 1)) : 0,
+        i + 1 < t.cur ? st.t0(i + 1) : 0};
+}
+__device__ __forceinline__ void wf_resume_ray(const f4* rec, trav_t& t, stack_t st) {
+  auto a = rec[0], b = rec[1], c = rec[2], d = rec[3], e = rec[4], f = rec[5];
+  t.o = {a.x, a.y, a.z}, t.d = {a.w, b.x, b.y};
+  t.dinv = {b.z, b.w, c.x}, t.wdinv = {c.y, c.z, c.w};
+  t.tmin = d.x, t.tmax = d.y, t.omax = d.z;
+  int bits = f2i(d.w);
+  t.plain = bits & 1, t.wplain = bits & 2, t.cull = bits & 4;
+  t.kind = f2i(e.x), t.inst = f2i(e.y), t.cur = f2i(e.z);
+  t.h = hit_t{f2i(e.w), f2i(f.x), {f.y, f.z}, f.w, (bits & 8) != 0};
+  for (int i = 0; i < t.cur; i += 2) {
+    auto s = rec[wf_susp_head + (i >> 1)];
+    st.push(i, f2i(s.x), s.y);
+    if (i + 1 < t.cur) st.push(i + 1, f2i(s.z), s.w);
+  }
+}
+
 // ---- kernels -----------------------------------------------------------------
 template <int S>
 __global__ void __launch_bounds__(wf_block)
@@ -250,7 +317,7 @@ __global__ void __launch_bounds__(wf_block)
                                             : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
     else
       material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);
-    cls = 2 + (material < wf_classes - 3 ? material : wf_classes - 3);
+    cls = 2 + (material < wf_classes - 4 ? material : wf_classes - 4);
     if (S == shader_volpathtrace && (f2i(a1.z) & wf_bit_vol)) cls = 1;
   }
   unsigned peers  = __match_any_sync(__activemask(), cls);
@@ -270,11 +337,15 @@ __global__ void __launch_bounds__(wf_block)
 // ends (ncu r01: 14.8 of 32 lanes live per traversal round, 10 of 32 in the SDF march).
 // Per ray the walk is the same sequence of operations, so hits are bit-identical.
 constexpr int wf_refill    = 8;
+#if !defined(VPT_WF_SUSPEND_AT)
+#define VPT_WF_SUSPEND_AT 20
+#endif
+constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in place)
 constexpr int wf_sdf_steps = 4;
 
 template <int S>
 __global__ void __launch_bounds__(wf_block, 7)
-    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur) {
+    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
   extern __shared__ int stack_mem[];
   constexpr bool sdf  = is_sdf_shader<S>();
   const unsigned full = 0xffffffffu;
@@ -282,8 +353,9 @@ __global__ void __launch_bounds__(wf_block, 7)
   int     lane  = threadIdx.x & 31;
   stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    w.counters->count_ext[cur ^ 1] = 0;
-    w.counters->count_pdf          = 0;
+    // count_ext[cur ^ 1] was reset by the previous iteration's k_wf_lightpdf: parked
+    // rays are appended to it while this kernel still runs
+    w.counters->count_pdf = 0;
     w.counters->rays_extend += (unsigned long long)count;
   }
   trav_t   t;
@@ -293,6 +365,15 @@ __global__ void __launch_bounds__(wf_block, 7)
   bool     has_ray = false;
   bool     more    = true;   // warp-uniform: the queue may still hold unclaimed entries
   bool     running = true;   // warp-uniform, the only exit
+  int      resumed = 0;
+  // Measured on B200: parking pays for sphere tracing (07_sdfunction 136 -> 100 ms
+  // per 16 spp), not for BVH walks, whose parked state is 20x larger and whose pixels' tail
+  // then lasts more iterations (03_volume 209 -> 217 ms); -DVPT_WF_SUSPEND_MESH opts in.
+#if defined(VPT_WF_SUSPEND_MESH)
+  const int suspend_mesh = suspend_at;
+#else
+  constexpr int suspend_mesh = 0;
+#endif
   t.cur       = 0;
   sp.finished = true;
   while (running) {
@@ -311,9 +392,18 @@ __global__ void __launch_bounds__(wf_block, 7)
         ray     = make_ray({a0.x, a0.y, a0.z}, {a0.w, a1.x, a1.y});
         if constexpr (sdf) {
           sp.begin(ray);
+          if (flags & wf_bit_susp) {
+            auto s = w.at(wf_hit, slot);
+            sp.t = s.x, sp.i = f2i(s.y);
+          }
         } else {
-          t.begin(sc, -1, ray, st);
+          if (flags & wf_bit_susp)
+            wf_resume_ray(w.susp[cur] + (size_t)f2i(w.at(wf_hit, slot).x) * w.susp_f4, t, st);
+          else
+            t.begin(sc, -1, ray, st);
         }
+        resumed += (flags & wf_bit_susp) ? 1 : 0;
+        flags &= ~wf_bit_susp;
         has_ray = true;
       }
     }
@@ -343,7 +433,7 @@ __global__ void __launch_bounds__(wf_block, 7)
                          : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
         else
           material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);
-        cls = 2 + (material < wf_classes - 3 ? material : wf_classes - 3);
+        cls = 2 + (material < wf_classes - 4 ? material : wf_classes - 4);
         if (S == shader_volpathtrace && (flags & wf_bit_vol)) cls = 1;
       }
       unsigned peers  = __match_any_sync(retiring, cls);
@@ -354,8 +444,36 @@ __global__ void __launch_bounds__(wf_block, 7)
       w.sort_key[qidx] = (cls << 24) | (base + __popc(peers & ((1u << lane) - 1)));
       has_ray = false;
     }
+    unsigned walking = __ballot_sync(full, has_ray);
+    if (!more && walking && __popc(walking) <= (sdf ? suspend_at : suspend_mesh)) {
+      // park what is left of this warp for the next iteration's launch
+      int n = __popc(walking), leader = __ffs(walking) - 1;
+      int rank = __popc(walking & ((1u << lane) - 1));
+      int rec = 0, at = 0, order = 0;
+      if (lane == leader) {
+        if constexpr (!sdf) rec = atomicAdd(&w.counters->susp_count[cur ^ 1], n);
+        at    = atomicAdd(&w.counters->count_ext[cur ^ 1], n);
+        order = atomicAdd(&w.counters->class_count[wf_class_susp], n);
+      }
+      rec = __shfl_sync(full, rec, leader), at = __shfl_sync(full, at, leader);
+      order = __shfl_sync(full, order, leader);
+      if (has_ray) {
+        if constexpr (sdf) {
+          w.at(wf_hit, slot) = {sp.t, i2f(sp.i), 0, 0};
+        } else {
+          wf_suspend_ray(w.susp[cur ^ 1] + (size_t)(rec + rank) * w.susp_f4, t, st);
+          w.at(wf_hit, slot).x = i2f(rec + rank);
+        }
+        w.at(wf_ray1, slot).z          = i2f(flags | wf_bit_susp);
+        w.queue_ext[cur ^ 1][at + rank] = slot;
+        w.sort_key[qidx]               = (wf_class_susp << 24) | (order + rank);
+        has_ray = false;
+      }
+    }
     running = more || __any_sync(full, has_ray);
   }
+  for (int o = 16; o > 0; o >>= 1) resumed += __shfl_down_sync(full, resumed, o);
+  if (lane == 0 && resumed) atomicAdd(&w.counters->rays_resumed, (unsigned long long)resumed);
 }
 
 // scatter the extend queue into class order (counting sort, second pass)
@@ -375,6 +493,8 @@ __global__ void __launch_bounds__(wf_block) k_wf_sort(wf_view w, int cur) {
   __syncthreads();
   int tid   = blockIdx.x * blockDim.x + threadIdx.x;
   int count = w.counters->count_ext[cur];
+  // parked rays sort last and are not shaded in this iteration
+  if (tid == 0) w.counters->count_shade = count - w.counters->class_count[wf_class_susp];
   if (tid >= count) return;
   int key = w.sort_key[tid];
   w.queue_shade[base[key >> 24] + (key & 0xffffff)] = w.queue_ext[cur][tid];
@@ -388,11 +508,14 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
     k_wf_shade(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
         rng_t* __restrict__ rngs, int cur) {
   int  tid      = blockIdx.x * blockDim.x + threadIdx.x;
-  int  count    = w.counters->count_ext[cur];
+  int  count    = w.counters->count_shade;
   bool to_ext   = false, to_pdf = false;
   int  slot     = 0;
   if (blockIdx.x == 0 && threadIdx.x < wf_classes) w.counters->class_count[threadIdx.x] = 0;
-  if (blockIdx.x == 0 && threadIdx.x == 0) w.counters->ext_head = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    w.counters->ext_head = 0;
+    w.counters->susp_count[cur] = 0;  // that pool was consumed by this iteration's extend
+  }
   if (tid < count) {
     slot    = w.queue_shade[tid];
     int idx = tile_pixel_index(slot, prm.width, prm.height);
@@ -432,7 +555,10 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
   int  count  = w.counters->count_pdf;
   bool to_ext = false;
   int  slot   = 0;
-  if (tid == 0) w.counters->rays_lightpdf += (unsigned long long)count;
+  if (tid == 0) {
+    w.counters->rays_lightpdf += (unsigned long long)count;
+    w.counters->count_ext[cur] = 0;  // consumed; the next iteration fills it
+  }
   if (tid < count) {
     slot    = w.queue_pdf[tid];
     int idx = tile_pixel_index(slot, prm.width, prm.height);
@@ -478,8 +604,30 @@ __global__ void __launch_bounds__(wf_block)
     wf_load_path<S>(w, slot, p, remaining);
     auto rng   = wf_load_rng(w, slot);
     auto alive = true;
+    bool parked = (f2i(w.at(wf_ray1, slot).z) & wf_bit_susp) != 0;
     while (alive) {  // single exit
-      auto      isec = find_hit<S>(sc, prm, p, st);
+      isect_t isec;
+      if (parked) {
+        // the slot's ray was parked by the last extend launch: finish that walk
+        auto ray = make_ray(p.o, p.d);
+        if constexpr (is_sdf_shader<S>()) {
+          sphere_t sp;
+          sp.begin(ray);
+          auto s = w.at(wf_hit, slot);
+          sp.t = s.x, sp.i = f2i(s.y);
+          while (!sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
+          isec = {sp.r.hit, sp.r.instance, sp.r.sdf, {0, 0}, sp.r.dist};
+        } else {
+          trav_t t;
+          wf_resume_ray(w.susp[cur] + (size_t)f2i(w.at(wf_hit, slot).x) * w.susp_f4, t, st);
+          while (!t.done()) t.round(sc, ray, st);
+          isec = {t.h.hit, t.h.instance, t.h.element, t.h.uv, t.h.distance};
+        }
+        parked = false;
+        n_ext -= 1;  // counted when it was first queued
+      } else {
+        isec = find_hit<S>(sc, prm, p, st);
+      }
       pending_t pd;
       auto      r = shade_hit<S>(sc, prm, p, rng, isec, pd);
       n_ext += 1;
@@ -596,6 +744,13 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     resident = per_sm * sms;
     if (resident <= 0) persistent = false;
   }
+  // lanes still walking at or below which a warp parks its rays once the queue is empty
+  static const char* susp_env = getenv("VPT_WF_SUSPEND");
+  int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
+  if (persistent) {
+    e = wf.reserve_suspended(resident * wf_block, wf_susp_record_f4(scene.stack_depth));
+    if (e != cudaSuccess) return e;
+  }
   auto  trace     = wf_trace::open();
   if (smem > 48 * 1024) {
     e = cudaFuncSetAttribute(k_wf_drain<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -608,7 +763,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (trace) trace->mark(grid);
       if (persistent)
         k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem>>>(scene.d,
-            prm, w, cur);
+            prm, w, cur, suspend_at);
       else
         k_wf_extend<S><<<grid, wf_block, smem>>>(scene.d, prm, w, cur);
       if (it == 0) cudaEventRecord(wf.k1);
@@ -645,7 +800,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   stats->top_kernel_ms       = (float)top_ms;
   stats->top_kernel_launches = top_launches;
   stats->top_kernel_units    = top_rays;
-  stats->rays_extend   = wf.host_counters->rays_extend;
+  stats->rays_extend   = wf.host_counters->rays_extend - wf.host_counters->rays_resumed;
   stats->rays_lightpdf = wf.host_counters->rays_lightpdf;
   return cudaGetLastError();
 }
