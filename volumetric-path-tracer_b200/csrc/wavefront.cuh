@@ -43,6 +43,12 @@
 namespace vpt {
 
 constexpr int wf_block   = 128;
+#if !defined(VPT_WF_PIPES)
+#define VPT_WF_PIPES 2
+#endif
+constexpr int wf_pipes   = VPT_WF_PIPES;        // independent wavefronts (streams) per render call
+constexpr int wf_pipes_min_slots = 1 << 16;  // smaller images run one pipe
+constexpr int wf_batch   = 8;  // iterations enqueued between two looks at the counters
 constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped), last: suspended
 constexpr int wf_class_susp = wf_classes - 1;
 
@@ -91,59 +97,96 @@ struct wf_view {
   int susp_f4;
 };
 
-struct wavefront_buffers {
-  bool         live     = false;
-  int          capacity = 0;
-  size_t       susp_bytes = 0;
+// One pipe = an independent wavefront over an interleaved share of the slots (tile t belongs
+// to pipe t % pipes), with its own queues, counters and CUDA stream. Two pipes let the
+// latency-bound kernels of one (shade, light pdf, the draining end of extend) run in the issue
+// slots the other leaves idle; pixels do not interact, so results do not depend on the split.
+constexpr int wf_max_pipes = 4;
+struct wf_pipe {
   wf_view      view{};
-  wf_counters* host_counters = nullptr;  // pinned
-  cudaEvent_t  poll = nullptr, k0 = nullptr, k1 = nullptr;
+  cudaStream_t stream = nullptr;
+  wf_counters* host_counters[2] = {nullptr, nullptr};  // pinned, one per batch in flight
+  cudaEvent_t  poll[2] = {nullptr, nullptr};
+  int*         queues = nullptr;
+  size_t       susp_bytes = 0;
+  // host-side progress
+  int active = 0, cur = 0, inflight = 0, batches = 0;
+  int polled_cur[2] = {0, 0};
+  bool draining = false;
+};
+
+struct wavefront_buffers {
+  bool        live     = false;
+  int         capacity = 0, pipes = 0;
+  f4*         rec = nullptr;
+  wf_pipe     pipe[wf_max_pipes];
+  cudaEvent_t k0 = nullptr, k1 = nullptr;
   void release() {
     if (!capacity) return;
-    cudaFree(view.rec);
-    cudaFree(view.queue_ext[0]);
-    cudaFree(view.counters);
-    if (view.susp[0]) cudaFree(view.susp[0]);
-    if (host_counters) cudaFreeHost(host_counters);
-    if (poll) cudaEventDestroy(poll);
+    cudaFree(rec);
+    for (auto& p : pipe) {
+      if (p.queues) cudaFree(p.queues);
+      if (p.view.counters) cudaFree(p.view.counters);
+      if (p.view.susp[0]) cudaFree(p.view.susp[0]);
+      for (int i = 0; i < 2; i++) {
+        if (p.host_counters[i]) cudaFreeHost(p.host_counters[i]);
+        if (p.poll[i]) cudaEventDestroy(p.poll[i]);
+      }
+      if (p.stream) cudaStreamDestroy(p.stream);
+    }
     if (k0) cudaEventDestroy(k0);
     if (k1) cudaEventDestroy(k1);
     *this = wavefront_buffers{};
   }
-  // `susp_records` suspended-ray records of `susp_f4` f4 each, per pool
+  // `susp_records` suspended-ray records of `susp_f4` f4 each, per pool and pipe
   cudaError_t reserve_suspended(int susp_records, int susp_f4) {
     size_t bytes = sizeof(f4) * (size_t)susp_f4 * (size_t)susp_records;
-    view.susp_f4 = susp_f4;
-    if (bytes <= susp_bytes) {
-      view.susp[1] = view.susp[0] + (size_t)susp_f4 * susp_records;
-      return cudaSuccess;
+    for (int i = 0; i < pipes; i++) {
+      auto& p = pipe[i];
+      p.view.susp_f4 = susp_f4;
+      if (bytes > p.susp_bytes) {
+        if (p.view.susp[0]) cudaFree(p.view.susp[0]);
+        p.view.susp[0] = p.view.susp[1] = nullptr, p.susp_bytes = 0;
+        auto e = cudaMalloc(&p.view.susp[0], 2 * bytes);
+        if (e != cudaSuccess) return e;
+        p.susp_bytes = bytes;
+      }
+      p.view.susp[1] = p.view.susp[0] + (size_t)susp_f4 * susp_records;
     }
-    if (view.susp[0]) cudaFree(view.susp[0]);
-    view.susp[0] = view.susp[1] = nullptr, susp_bytes = 0;
-    auto e = cudaMalloc(&view.susp[0], 2 * bytes);
-    if (e != cudaSuccess) return e;
-    view.susp[1] = view.susp[0] + (size_t)susp_f4 * susp_records;
-    susp_bytes   = bytes;
     return cudaSuccess;
   }
-  cudaError_t reserve(int slots) {
-    if (capacity >= slots) return cudaSuccess;
+  // slots of pipe i: whole tiles (32 slots), tile t -> pipe t % npipes
+  static int pipe_slots(int slots, int npipes, int i) {
+    int tiles = slots / 32;
+    return ((tiles - i + npipes - 1) / npipes) * 32;
+  }
+  cudaError_t reserve(int slots, int npipes) {
+    if (capacity >= slots && pipes == npipes) return cudaSuccess;
     release();
-    auto e = cudaMalloc(&view.rec, sizeof(f4) * wf_rec * (size_t)slots);
+    auto e = cudaMalloc(&rec, sizeof(f4) * wf_rec * (size_t)slots);
     if (e != cudaSuccess) return e;
-    int* q = nullptr;
-    e      = cudaMalloc(&q, sizeof(int) * 5 * (size_t)slots);
-    if (e != cudaSuccess) return e;
-    view.queue_ext[0] = q, view.queue_ext[1] = q + slots, view.queue_pdf = q + 2 * (size_t)slots;
-    view.queue_shade = q + 3 * (size_t)slots, view.sort_key = q + 4 * (size_t)slots;
-    e = cudaMalloc(&view.counters, sizeof(wf_counters));
-    if (e == cudaSuccess) e = cudaMallocHost(&host_counters, sizeof(wf_counters));
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&poll, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreate(&k0);
+    capacity = slots, pipes = npipes;  // from here on release() frees what exists
+    for (int i = 0; i < npipes; i++) {
+      auto&  p = pipe[i];
+      size_t n = (size_t)pipe_slots(slots, npipes, 0);
+      e = cudaMalloc(&p.queues, sizeof(int) * 5 * n);
+      if (e != cudaSuccess) return e;
+      auto q = p.queues;
+      p.view.rec = rec;
+      p.view.queue_ext[0] = q, p.view.queue_ext[1] = q + n, p.view.queue_pdf = q + 2 * n;
+      p.view.queue_shade = q + 3 * n, p.view.sort_key = q + 4 * n;
+      e = cudaMalloc(&p.view.counters, sizeof(wf_counters));
+      for (int k = 0; k < 2 && e == cudaSuccess; k++) {
+        e = cudaMallocHost(&p.host_counters[k], sizeof(wf_counters));
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p.poll[k], cudaEventDisableTiming);
+      }
+      // blocking streams: ordered against the legacy default stream the caller's events use
+      if (e == cudaSuccess) e = cudaStreamCreate(&p.stream);
+      if (e != cudaSuccess) return e;
+    }
+    e = cudaEventCreate(&k0);
     if (e == cudaSuccess) e = cudaEventCreate(&k1);
-    if (e != cudaSuccess) return e;
-    capacity = slots;
-    return cudaSuccess;
+    return e;
   }
 };
 
@@ -269,8 +312,9 @@ __device__ __forceinline__ void wf_resume_ray(const f4* rec, trav_t& t, stack_t 
 template <int S>
 __global__ void __launch_bounds__(wf_block)
     k_wf_init(const DScene sc, const DParams prm, wf_view w, rng_t* __restrict__ rngs, int slots,
-        int nsamples) {
-  int  slot   = blockIdx.x * blockDim.x + threadIdx.x;
+        int nsamples, int pipe, int npipes) {
+  int  tid    = blockIdx.x * blockDim.x + threadIdx.x;
+  int  slot   = (((tid >> 5) * npipes + pipe) << 5) | (tid & 31);  // this pipe's tiles
   bool active = false;
   if (slot < slots) {
     int idx = tile_pixel_index(slot, prm.width, prm.height);
@@ -336,7 +380,13 @@ __global__ void __launch_bounds__(wf_block)
 // `wf_refill` lanes idle. A fixed ray-per-lane launch keeps a warp busy until its slowest ray
 // ends (ncu r01: 14.8 of 32 lanes live per traversal round, 10 of 32 in the SDF march).
 // Per ray the walk is the same sequence of operations, so hits are bit-identical.
-constexpr int wf_refill    = 8;
+#if !defined(VPT_WF_REFILL)
+#define VPT_WF_REFILL 8
+#endif
+#if !defined(VPT_EXT_BLOCKS)
+#define VPT_EXT_BLOCKS 6
+#endif
+constexpr int wf_refill    = VPT_WF_REFILL;
 #if !defined(VPT_WF_SUSPEND_AT)
 #define VPT_WF_SUSPEND_AT 20
 #endif
@@ -344,7 +394,7 @@ constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in plac
 constexpr int wf_sdf_steps = 4;
 
 template <int S>
-__global__ void __launch_bounds__(wf_block, 7)
+__global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
     k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
   extern __shared__ int stack_mem[];
   constexpr bool sdf  = is_sdf_shader<S>();
@@ -705,9 +755,16 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     vpt_trace_stats* stats) {
   int slots = tile_slot_count(prm.width, prm.height);
   if (slots >= (1 << 24)) return cudaErrorInvalidValue;  // sort_key packs the rank in 24 bits
-  auto e = wf.reserve(slots);
+  auto trace = wf_trace::open();
+  // pipes: VPT_WF_PIPES overrides; small images, traced runs and sphere tracing (whose extend
+  // keeps the issue slots 88 % busy on its own: B200, 07_sdfunction 140 vs 136 Mpaths/s) use one
+  static const char* pipes_env = getenv("VPT_WF_PIPES");
+  int npipes = pipes_env ? atoi(pipes_env)
+                         : (slots >= wf_pipes_min_slots && !is_sdf_shader<S>() ? wf_pipes : 1);
+  npipes     = npipes < 1 ? 1 : (npipes > wf_max_pipes ? wf_max_pipes : npipes);
+  if (trace) npipes = 1;
+  auto e = wf.reserve(slots, npipes);
   if (e != cudaSuccess) return e;
-  auto&  w    = wf.view;
   size_t smem = (size_t)scene.stack_depth * vpt_stack_words * wf_block * sizeof(int);
   if (smem > 48 * 1024) {
     e = cudaFuncSetAttribute(k_wf_extend<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -717,21 +774,11 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(k_wf_lightpdf<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
           (int)smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(k_wf_drain<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  e = cudaMemsetAsync(w.counters, 0, sizeof(wf_counters));
-  if (e != cudaSuccess) return e;
-  int grid_all = (slots + wf_block - 1) / wf_block;
-  k_wf_init<S><<<grid_all, wf_block>>>(scene.d, prm, w, rngs, slots, nsamples);
-  *launches    = 1;
-  int   active = slots, cur = 0;
-  // the first extend launch after every poll is timed with CUDA events: its ray count
-  // (`active`) is known exactly, so the pairs give the dominant kernel's rays per second
-  double             top_ms = 0;
-  unsigned long long top_rays = 0;
-  int                top_launches = 0;
-  int   drain_at  = wf_drain_threshold(slots);
-  // persistent extend (mesh shaders): as many blocks as the device keeps resident
+  // persistent extend: as many blocks as the device keeps resident
   bool persistent = !getenv("VPT_WF_NO_PERSISTENT");
   int  resident   = 0;
   if (persistent) {
@@ -742,6 +789,10 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
         smem);
     if (e != cudaSuccess) return e;
     resident = per_sm * sms;
+    // VPT_WF_EXT_BLOCKS=<n>: resident extend blocks per SM (experiments: leaves room for the
+    // other pipe's kernels next to a running extend)
+    static const char* blocks_env = getenv("VPT_WF_EXT_BLOCKS");
+    if (blocks_env && atoi(blocks_env) > 0 && atoi(blocks_env) < per_sm) resident = atoi(blocks_env) * sms;
     if (resident <= 0) persistent = false;
   }
   // lanes still walking at or below which a warp parks its rays once the queue is empty
@@ -751,57 +802,123 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     e = wf.reserve_suspended(resident * wf_block, wf_susp_record_f4(scene.stack_depth));
     if (e != cudaSuccess) return e;
   }
-  auto  trace     = wf_trace::open();
-  if (smem > 48 * 1024) {
-    e = cudaFuncSetAttribute(k_wf_drain<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  *launches = 0;
+  // the first extend launch of every batch of pipe 0 is timed with CUDA events: its ray count
+  // is known exactly, so the pairs give the dominant kernel's rays per second (with two
+  // pipes the other pipe's kernels share the device during that time, as they do in the run)
+  double             top_ms = 0;
+  unsigned long long top_rays = 0;
+  int                top_launches = 0, timed_active = 0, timed_batch = 0;
+  bool               timed_pending = false;
+
+  for (int i = 0; i < npipes; i++) {
+    auto& p  = wf.pipe[i];
+    int   ps = wavefront_buffers::pipe_slots(slots, npipes, i);
+    e = cudaMemsetAsync(p.view.counters, 0, sizeof(wf_counters), p.stream);
     if (e != cudaSuccess) return e;
+    if (ps > 0)
+      k_wf_init<S><<<(ps + wf_block - 1) / wf_block, wf_block, 0, p.stream>>>(scene.d, prm, p.view,
+          rngs, slots, nsamples, i, npipes);
+    *launches += 1;
+    p.active = ps, p.cur = 0, p.inflight = 0, p.batches = 0, p.draining = false;
   }
-  while (active > 0) {
-    int grid = (active + wf_block - 1) / wf_block;
-    for (int it = 0; it < 8; it++) {
-      if (it == 0) cudaEventRecord(wf.k0);
+  int drain_at = wf_drain_threshold(slots) / npipes;
+
+  // one batch = wf_batch iterations, then a snapshot of the counters; two batches per pipe
+  // are kept in flight so that a stream never runs dry while the host reads a snapshot
+  auto enqueue = [&](int i) -> cudaError_t {
+    auto& p    = wf.pipe[i];
+    auto& w    = p.view;
+    int   grid = (p.active + wf_block - 1) / wf_block;
+    bool  timed = i == 0 && !timed_pending;
+    for (int it = 0; it < wf_batch; it++) {
+      if (it == 0 && timed) cudaEventRecord(wf.k0, p.stream);
       if (trace) trace->mark(grid);
       if (persistent)
-        k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem>>>(scene.d,
-            prm, w, cur, suspend_at);
+        k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
+            scene.d, prm, w, p.cur, suspend_at);
       else
-        k_wf_extend<S><<<grid, wf_block, smem>>>(scene.d, prm, w, cur);
-      if (it == 0) cudaEventRecord(wf.k1);
-      k_wf_sort<<<grid, wf_block>>>(w, cur);
+        k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+      if (it == 0 && timed) cudaEventRecord(wf.k1, p.stream);
+      k_wf_sort<<<grid, wf_block, 0, p.stream>>>(w, p.cur);
       if (trace) trace->mark(grid);
-      k_wf_shade<S><<<grid, wf_block>>>(scene.d, prm, w, image, rngs, cur);
+      k_wf_shade<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
       if (trace) trace->mark(grid);
-      k_wf_lightpdf<S><<<grid, wf_block, smem>>>(scene.d, prm, w, image, rngs, cur);
+      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
       if (trace) trace->mark(grid);
-      cur ^= 1;
+      p.cur ^= 1;
       *launches += 4;
     }
-    e = cudaMemcpyAsync(wf.host_counters, w.counters, sizeof(wf_counters), cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) return e;
-    e = cudaEventRecord(wf.poll);
-    if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
-    if (e != cudaSuccess) return e;
-    float ms = 0;
-    if (cudaEventElapsedTime(&ms, wf.k0, wf.k1) == cudaSuccess)
-      top_ms += ms, top_rays += (unsigned long long)active, top_launches += 1;
-    active = wf.host_counters->count_ext[cur];
-    if (active > 0 && active <= drain_at) {
-      grid = (active + wf_block - 1) / wf_block;
-      k_wf_drain<S><<<grid, wf_block, smem>>>(scene.d, prm, w, image, rngs, cur);
-      *launches += 1;
-      e = cudaMemcpyAsync(wf.host_counters, w.counters, sizeof(wf_counters), cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess) e = cudaEventRecord(wf.poll);
-      if (e == cudaSuccess) e = cudaEventSynchronize(wf.poll);
+    if (timed) timed_pending = true, timed_active = p.active, timed_batch = p.batches;
+    int  k = p.batches & 1;
+    auto e = cudaMemcpyAsync(p.host_counters[k], w.counters, sizeof(wf_counters),
+        cudaMemcpyDeviceToHost, p.stream);
+    if (e == cudaSuccess) e = cudaEventRecord(p.poll[k], p.stream);
+    p.polled_cur[k] = p.cur;
+    p.batches += 1, p.inflight += 1;
+    return e;
+  };
+  auto drain = [&](int i) -> cudaError_t {
+    auto& p    = wf.pipe[i];
+    int   grid = (p.active + wf_block - 1) / wf_block;
+    k_wf_drain<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, p.view, image, rngs, p.cur);
+    *launches += 1;
+    int  k = p.batches & 1;
+    auto e = cudaMemcpyAsync(p.host_counters[k], p.view.counters, sizeof(wf_counters),
+        cudaMemcpyDeviceToHost, p.stream);
+    if (e == cudaSuccess) e = cudaEventRecord(p.poll[k], p.stream);
+    p.batches += 1, p.inflight += 1;
+    p.draining = true;
+    return e;
+  };
+  int  depth = npipes > 1 ? 2 : 1;
+  bool busy  = true;
+  while (busy) {
+    busy = false;
+    for (int i = 0; i < npipes; i++) {
+      auto& p = wf.pipe[i];
+      if (p.active <= 0 || p.draining) continue;
+      if (p.active <= drain_at) {
+        // few slots left: once the batches in flight are done, one launch finishes them
+        if (p.inflight == 0) e = drain(i);
+      } else {
+        while (e == cudaSuccess && p.inflight < depth) e = enqueue(i);
+      }
       if (e != cudaSuccess) return e;
-      active = 0;
+    }
+    for (int i = 0; i < npipes; i++) {
+      auto& p = wf.pipe[i];
+      if (p.inflight == 0) continue;
+      busy       = true;
+      int batch  = p.batches - p.inflight;  // oldest batch in flight
+      int k      = batch & 1;
+      e          = cudaEventSynchronize(p.poll[k]);
+      if (e != cudaSuccess) return e;
+      p.inflight -= 1;
+      if (p.draining) {
+        p.active = 0;
+        continue;
+      }
+      if (i == 0 && timed_pending && batch == timed_batch) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, wf.k0, wf.k1) == cudaSuccess)
+          top_ms += ms, top_rays += (unsigned long long)timed_active, top_launches += 1;
+        timed_pending = false;
+      }
+      int count = p.host_counters[k]->count_ext[p.polled_cur[k]];
+      p.active  = count < p.active ? count : p.active;
     }
   }
   if (trace) trace->dump();
   stats->top_kernel_ms       = (float)top_ms;
   stats->top_kernel_launches = top_launches;
   stats->top_kernel_units    = top_rays;
-  stats->rays_extend   = wf.host_counters->rays_extend - wf.host_counters->rays_resumed;
-  stats->rays_lightpdf = wf.host_counters->rays_lightpdf;
+  stats->rays_extend = stats->rays_lightpdf = 0;
+  for (int i = 0; i < npipes; i++) {
+    auto c = wf.pipe[i].host_counters[(wf.pipe[i].batches - 1) & 1];
+    stats->rays_extend += c->rays_extend - c->rays_resumed;
+    stats->rays_lightpdf += c->rays_lightpdf;
+  }
   return cudaGetLastError();
 }
 
