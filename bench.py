@@ -83,8 +83,9 @@ EXTEND = {
     "05_head1ss": dict(box_tests=40.69, tri_tests=4.78, inst_transforms=0.62, prim_bytes=48),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend_persistent
-# launch, from profiles/r01_ncu_full_final.brief.txt (ncu --set full), per launch like `achieved`
-NCU_TRAFFIC = {"03_volume": 93.0e6 + 27.5e6}
+# launch (one of the two pipes: 341 k rays), from profiles/r01d_ncu_full.brief.txt (ncu --set full),
+# per launch like `achieved`
+NCU_TRAFFIC = {"03_volume": 46.1e6 + 6.7e6}
 
 
 def extend_flops_per_ray(name):
@@ -309,6 +310,20 @@ def gpu_arm(args, wl, rank, world, local_rank):
     del host_img
     pix = r.width * r.height
 
+    # ---- the dominant kernel on its own (untimed extra call, one pipe) ---------------------------
+    # In the timed region two wavefront pipes share the device, so the event pair around an extend
+    # launch also spans the other pipe's kernels. One more call with a single pipe gives the
+    # kernel's own rate; it is reported beside the timed-region figure, never instead of it.
+    alone = None
+    if rank == 0 and "VPT_WF_PIPES" not in os.environ:
+        os.environ["VPT_WF_PIPES"] = "1"
+        r.reset(rng_offset)
+        r.trace(spp)
+        st = r.stats()
+        del os.environ["VPT_WF_PIPES"]
+        if st.top_kernel_launches > 0 and st.top_kernel_ms > 0:
+            alone = (st.top_kernel_ms, st.top_kernel_units, st.top_kernel_launches)
+
     # ---- max over ranks -----------------------------------------------------------------------
     times = torch.tensor([total_ms + reduce_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -336,7 +351,18 @@ def gpu_arm(args, wl, rank, world, local_rank):
                           "avg_rays_per_launch": top_units / top_launches,
                           "grays_per_s": top_units / (top_ms / 1e3) / 1e9,
                           "flops_per_ray": extend_flops_per_ray(args.workload),
-                          "algorithmic_bytes_per_ray": extend_bytes_per_ray(args.workload)}
+                          "algorithmic_bytes_per_ray": extend_bytes_per_ray(args.workload),
+                          "note": "timed region: the other wavefront pipe's kernels share the device "
+                                  "during these launches"}
+            if alone is not None:
+                a_ms, a_units, a_n = alone
+                a_tflops = extend_flops_per_ray(args.workload) * a_units / (a_ms / 1e3) / 1e12
+                per_launch["alone"] = {"sampled_launches": a_n, "avg_launch_us": 1e3 * a_ms / a_n,
+                                       "avg_rays_per_launch": a_units / a_n,
+                                       "grays_per_s": a_units / (a_ms / 1e3) / 1e9,
+                                       "achieved": a_tflops, "frac": a_tflops / fp32_peak,
+                                       "note": "one untimed extra call with a single pipe "
+                                               "(VPT_WF_PIPES=1): the kernel with the device to itself"}
         else:
             kernel, achieved, per_launch = "whole step", step_tflops, None
         line = {

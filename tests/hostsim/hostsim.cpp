@@ -30,7 +30,7 @@ using namespace vpt;
 template <int S>
 static void render_rows(const DScene& sc, const DParams& prm, pathtrace_state& state, int nsamples,
     int tid, int nthreads) {
-  int  stack_mem[vpt_stack_depth * vpt_stack_words];
+  alignas(8) int stack_mem[vpt_stack_depth * vpt_stack_words];
   auto st = stack_t{stack_mem, 1};
   for (int idx = tid; idx < state.width * state.height; idx += nthreads) {
     auto rng = rng_t{state.rngs[idx].state, state.rngs[idx].inc};
@@ -171,7 +171,7 @@ int main(int argc, const char** argv) {
     auto fl   = std::vector<float>(n * 3);
     auto sid  = std::vector<int>(n * 3);
     auto sfl  = std::vector<float>(n * 4);
-    int  stack_mem[vpt_stack_depth * vpt_stack_words];
+    alignas(8) int stack_mem[vpt_stack_depth * vpt_stack_words];
     auto st      = stack_t{stack_mem, 1};
     auto has_sdf = sc.num_sdfs + sc.num_vol_instances > 0;
     for (size_t i = 0; i < n; i++) {

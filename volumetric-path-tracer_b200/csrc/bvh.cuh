@@ -54,18 +54,28 @@ namespace vpt {
 #if defined(VPT_STACK_CHECK)
 inline int vpt_stack_high_water = -1;  // tests/hostsim only
 #endif
+struct alignas(8) int2_t {
+  int x, y;
+};
 struct stack_t {
   int* base;
   int  stride;
-  // entry i = two words: the ref at row 2 i, its t0 at row 2 i + 1
-  VPT_FN int   ref(int i) const { return base[2 * i * stride]; }
-  VPT_FN float t0(int i) const { return i2f(base[(2 * i + 1) * stride]); }
+  // entry i = {ref, t0} as one 8-byte word at column offset 2 i stride (one LDS.64 / STS.64)
+  struct entry_t {
+    int   ref;
+    float t0;
+  };
+  VPT_FN entry_t get(int i) const {
+    auto v = *reinterpret_cast<const int2_t*>(base + 2 * i * stride);
+    return {v.x, i2f(v.y)};
+  }
+  VPT_FN int   ref(int i) const { return get(i).ref; }
+  VPT_FN float t0(int i) const { return get(i).t0; }
   VPT_FN void  push(int i, int r, float t) const {
 #if defined(VPT_STACK_CHECK)
     if (i > vpt_stack_high_water) vpt_stack_high_water = i;
 #endif
-    base[2 * i * stride]       = r;
-    base[(2 * i + 1) * stride] = f2i(t);
+    *reinterpret_cast<int2_t*>(base + 2 * i * stride) = int2_t{r, f2i(t)};
   }
 };
 constexpr int vpt_stack_words = 2;  // ints per entry (sizes the shared-memory columns)
@@ -214,8 +224,9 @@ struct trav_t {
     int pops = trav_pops;
     while (cur != 0 && leaf == 0 && enter < 0 && pops != 0) {
       pops--;
-      int   e  = st.ref(--cur);
-      float te = st.t0(cur);
+      auto  en = st.get(--cur);
+      int   e  = en.ref;
+      float te = en.t0;
       if (e >= 0) {
         if (te <= tmax * box_slack) {
           VPT_WORK(node_visits, 1);
@@ -320,7 +331,7 @@ VPT_FN hit_t traverse(const DScene& sc, int first, const ray3& ray, stack_t st) 
 
 #if defined(VPT_CULL_CHECK)
 inline void vpt_cull_check(const DScene& sc, int instance, const ray3& ray, float tmax) {
-  int  mem[vpt_stack_depth * vpt_stack_words];
+  alignas(8) int mem[vpt_stack_depth * vpt_stack_words];
   auto r = ray;
   r.tmax = tmax;
   VPT_WORK(culled, 1);

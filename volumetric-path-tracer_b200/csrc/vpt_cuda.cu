@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(mega_block)
   int tid = blockIdx.x * blockDim.x + threadIdx.x;
   int idx = tile_pixel_index(tid, prm.width, prm.height);
   if (idx < 0) return;
-  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
   auto    rng = rngs[idx];
   auto    acc = image[idx];
   for (int s = 0; s < nsamples; s++) {
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(mega_block)
   extern __shared__ int stack_mem[];
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
   auto    r   = rays + 8 * (size_t)i;
   auto    ray = ray3{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}, r[6], r[7]};
   auto    h   = instance >= 0 ? intersect_instance(sc, instance, ray, st)

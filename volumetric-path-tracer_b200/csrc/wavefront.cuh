@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(wf_block)
   }
   if (tid >= count) return;
   int     slot = w.queue_ext[cur][tid];
-  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
   auto    a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
   path_t  p;
   p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
   const unsigned full = 0xffffffffu;
   int     count = w.counters->count_ext[cur];
   int     lane  = threadIdx.x & 31;
-  stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // count_ext[cur ^ 1] was reset by the previous iteration's k_wf_lightpdf: parked
     // rays are appended to it while this kernel still runs
@@ -612,7 +612,7 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
   if (tid < count) {
     slot    = w.queue_pdf[tid];
     int idx = tile_pixel_index(slot, prm.width, prm.height);
-    stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+    stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
     path_t  p;
     int     remaining;
     wf_load_path<S>(w, slot, p, remaining);
@@ -648,7 +648,7 @@ __global__ void __launch_bounds__(wf_block)
   if (tid < count) {
     int     slot = w.queue_ext[cur][tid];
     int     idx  = tile_pixel_index(slot, prm.width, prm.height);
-    stack_t st{stack_mem + threadIdx.x, (int)blockDim.x};
+    stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
     path_t  p;
     int     remaining;
     wf_load_path<S>(w, slot, p, remaining);
@@ -758,7 +758,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   auto trace = wf_trace::open();
   // pipes: VPT_WF_PIPES overrides; small images, traced runs and sphere tracing (whose extend
   // keeps the issue slots 88 % busy on its own: B200, 07_sdfunction 140 vs 136 Mpaths/s) use one
-  static const char* pipes_env = getenv("VPT_WF_PIPES");
+  const char* pipes_env = getenv("VPT_WF_PIPES");  // read per call: bench.py samples one pipe alone
   int npipes = pipes_env ? atoi(pipes_env)
                          : (slots >= wf_pipes_min_slots && !is_sdf_shader<S>() ? wf_pipes : 1);
   npipes     = npipes < 1 ? 1 : (npipes > wf_max_pipes ? wf_max_pipes : npipes);
