@@ -220,6 +220,14 @@ struct trav_t {
   // bound keeps lanes that already hold work from waiting on the lane with the longest
   // descent; it changes the SIMT schedule only.
   VPT_FN void round(const DScene& sc, const ray3& ray, stack_t st) {
+    int leaf = descend(sc, ray, st);
+    if (leaf != 0) test_leaf(sc, leaf);
+  }
+
+  // The descent of one round. Returns the mesh leaf this lane now holds (0: none); the
+  // caller tests its primitives, alone (test_leaf) or together with the other lanes of the
+  // warp (wavefront.cuh, wf_test_leaves_warp).
+  VPT_FN int descend(const DScene& sc, const ray3& ray, stack_t st) {
     int leaf = 0, enter = -1;
     int pops = trav_pops;
     while (cur != 0 && leaf == 0 && enter < 0 && pops != 0) {
@@ -280,37 +288,42 @@ struct trav_t {
         }
       }
     }
-    // leaves: primitives in stored order; a scene leaf queues its instances
-    if (leaf != 0) {
+    // a scene leaf queues its instances (reverse order, so that they pop in leaf order)
+    if (leaf != 0 && kind < 0) {
       int lstart = leaf >> 3, lnum = leaf & 7;
-      if (kind == kind_quads) {
-        for (auto i = 0; i < lnum; i++) {
-          auto p = sc.prims + lstart + 4 * i;
-          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), q = ld4(p + 3);
-          if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(q), h.uv, h.distance)) {
-            h.hit = true, h.instance = inst, h.element = f2i(a.w);
-            tmax = h.distance;
-          }
-        }
-      } else if (kind >= 0) {
-        for (auto i = 0; i < lnum; i++) {
-          auto p = sc.prims + lstart + 3 * i;
-          auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
-          if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), h.uv, h.distance)) {
-            h.hit = true, h.instance = inst, h.element = f2i(a.w);
-            tmax = h.distance;
-          }
-        }
-      } else {
-        // reverse order, so that the instances pop in leaf order
-        for (auto i = lnum - 1; i >= 0; i--) {
-          auto p  = sc.scene_leaves + 2 * (lstart + i);
-          auto b0 = ld4(p), b1 = ld4(p + 1);
-          bool skip = cull && omax <= b1.w && misses_instance_box(o, dinv, tmin, tmax, b0, b1);
+      for (auto i = lnum - 1; i >= 0; i--) {
+        auto p  = sc.scene_leaves + 2 * (lstart + i);
+        auto b0 = ld4(p), b1 = ld4(p + 1);
+        bool skip = cull && omax <= b1.w && misses_instance_box(o, dinv, tmin, tmax, b0, b1);
 #if defined(VPT_CULL_CHECK)
-          if (skip && vpt_cull_check_on) vpt_cull_check(sc, f2i(b1.z), ray, tmax);
+        if (skip && vpt_cull_check_on) vpt_cull_check(sc, f2i(b1.z), ray, tmax);
 #endif
-          if (!skip) st.push(cur++, make_ref(f2i(b1.z), ref_instance), 0);
+        if (!skip) st.push(cur++, make_ref(f2i(b1.z), ref_instance), 0);
+      }
+      leaf = 0;
+    }
+    return leaf;
+  }
+
+  // mesh leaf: primitives in stored order, `t <= tmax` accepts
+  VPT_FN void test_leaf(const DScene& sc, int leaf) {
+    int lstart = leaf >> 3, lnum = leaf & 7;
+    if (kind == kind_quads) {
+      for (auto i = 0; i < lnum; i++) {
+        auto p = sc.prims + lstart + 4 * i;
+        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), q = ld4(p + 3);
+        if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(q), h.uv, h.distance)) {
+          h.hit = true, h.instance = inst, h.element = f2i(a.w);
+          tmax = h.distance;
+        }
+      }
+    } else {
+      for (auto i = 0; i < lnum; i++) {
+        auto p = sc.prims + lstart + 3 * i;
+        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
+        if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), h.uv, h.distance)) {
+          h.hit = true, h.instance = inst, h.element = f2i(a.w);
+          tmax = h.distance;
         }
       }
     }

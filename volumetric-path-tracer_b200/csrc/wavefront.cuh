@@ -308,6 +308,83 @@ __device__ __forceinline__ void wf_resume_ray(const f4* rec, trav_t& t, stack_t 
   }
 }
 
+// ---- leaf tests shared by the warp ----------------------------------------------------
+// After a descent only some lanes hold a leaf, each with 1..4 primitives; tested lane by
+// lane the warp runs the (long) primitive test 3-4 times at ~5 of 32 lanes (ncu r01c). Here
+// the (lane, primitive) pairs of the whole warp are laid out densely, one per lane: a lane
+// fetches the owner's ray with shuffles, tests ONE primitive against the owner's tmax, and
+// every owner then folds its primitives' distances in stored order with `t <= tmax`, exactly
+// as the sequential loop does (each test sees a tmax no smaller than the sequential one, so
+// it reports a superset of hits with the same distances; the fold rejects the surplus and
+// the later of two equal distances still wins).
+// Measured on B200: no gain (03_volume 181.5 ms per 64 spp with it, 177.8 ms without: the ten
+// shuffles per pass, the fold and 58 bytes of spills cost what the denser tests save), so the
+// per-lane loop stays the default and this path is opt-in (-DVPT_WF_COOP_LEAVES); it passes the
+// same bit-exact parity suite.
+#if defined(VPT_WF_COOP_LEAVES)
+__device__ __forceinline__ void wf_test_leaves_warp(const DScene& sc, trav_t& t, int leaf,
+    unsigned char* tab) {
+  const unsigned full = 0xffffffffu;
+  if (__ballot_sync(full, leaf != 0) == 0) return;
+  int lane = threadIdx.x & 31;
+  int n    = leaf != 0 ? (leaf & 7) : 0;
+  int incl = n;
+  for (int o = 1; o < 32; o <<= 1) {
+    int v = __shfl_up_sync(full, incl, o);
+    if (lane >= o) incl += v;
+  }
+  int total = __shfl_sync(full, incl, 31);
+  int nmax  = __reduce_max_sync(full, n);
+  int excl  = incl - n;
+  for (int k = 0; k < n; k++) tab[excl + k] = (unsigned char)(lane | (k << 5));
+  __syncwarp();
+  int lstart = leaf >> 3;
+  for (int base = 0; base < total; base += 32) {  // warp-uniform
+    int  item  = base + lane;
+    bool valid = item < total;
+    int  code  = valid ? tab[item] : lane;
+    int  src = code & 31, k = code >> 5;
+    f3    o  = {__shfl_sync(full, t.o.x, src), __shfl_sync(full, t.o.y, src), __shfl_sync(full, t.o.z, src)};
+    f3    d  = {__shfl_sync(full, t.d.x, src), __shfl_sync(full, t.d.y, src), __shfl_sync(full, t.d.z, src)};
+    float tmin = __shfl_sync(full, t.tmin, src), tmax = __shfl_sync(full, t.tmax, src);
+    int   kind = __shfl_sync(full, t.kind, src), ls = __shfl_sync(full, lstart, src);
+    float rt = __int_as_float(0x7fc00000);  // NaN: no hit (fails `rt <= tmax`)
+    f2    ruv = {0, 0};
+    int   relem = -1;
+    if (valid) {
+      float dist;
+      if (kind == kind_quads) {
+        auto p = sc.prims + ls + 4 * k;
+        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2), q = ld4(p + 3);
+        if (intersect_quad(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), xyz(q), ruv, dist))
+          rt = dist, relem = f2i(a.w);
+      } else {
+        auto p = sc.prims + ls + 3 * k;
+        auto a = ld4(p), b = ld4(p + 1), c = ld4(p + 2);
+        if (intersect_triangle(o, d, tmin, tmax, xyz(a), xyz(b), xyz(c), ruv, dist))
+          rt = dist, relem = f2i(a.w);
+      }
+    }
+    // owners fold the items of this pass that are theirs, in stored order
+    int win = -1;
+    for (int k2 = 0; k2 < nmax; k2++) {  // warp-uniform
+      int   it   = excl + k2;
+      bool  mine = k2 < n && it >= base && it < base + 32;
+      float tt   = __shfl_sync(full, rt, mine ? it - base : lane);
+      if (mine && tt <= t.tmax) t.tmax = tt, win = it - base;
+    }
+    int   from = win >= 0 ? win : lane;
+    float u = __shfl_sync(full, ruv.x, from), v = __shfl_sync(full, ruv.y, from);
+    int   el = __shfl_sync(full, relem, from);
+    if (win >= 0) {
+      t.h.hit = true, t.h.instance = t.inst, t.h.element = el;
+      t.h.uv = {u, v}, t.h.distance = t.tmax;
+    }
+  }
+  __syncwarp();  // the table is rewritten next round
+}
+#endif
+
 // ---- kernels -----------------------------------------------------------------
 template <int S>
 __global__ void __launch_bounds__(wf_block)
@@ -397,6 +474,9 @@ template <int S>
 __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
     k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
   extern __shared__ int stack_mem[];
+#if defined(VPT_WF_COOP_LEAVES)
+  __shared__ unsigned char leaf_tab[wf_block / 32][32 * 8];
+#endif
   constexpr bool sdf  = is_sdf_shader<S>();
   const unsigned full = 0xffffffffu;
   int     count = w.counters->count_ext[cur];
@@ -461,7 +541,13 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
       for (int k = 0; k < wf_sdf_steps; k++)
         if (has_ray && !sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
     } else {
+#if !defined(VPT_WF_COOP_LEAVES)
       if (has_ray && !t.done()) t.round(sc, ray, st);
+#else
+      int leaf = 0;
+      if (has_ray && !t.done()) leaf = t.descend(sc, ray, st);
+      wf_test_leaves_warp(sc, t, leaf, leaf_tab[threadIdx.x >> 5]);
+#endif
     }
     bool     retire   = has_ray && (sdf ? sp.done() : t.done());
     unsigned retiring = __ballot_sync(full, retire);
