@@ -14,6 +14,8 @@
  *                               (libs/yocto_pathtrace/yocto_pathtrace.cpp:1052-1054);
  *                               inputs are the outputs of make_bvh (:955) and
  *                               make_lights (:983)
+ *   vpt_cuda_upload_scene_device_lights
+ *                            <- the same, with make_lights (:983-1049) run on the device
  *   vpt_cuda_create_state    <- make_state (yocto_pathtrace.cpp:960-980): image / rngs
  *   vpt_cuda_trace_samples   <- pathtrace_samples (yocto_pathtrace.cpp:1052-1092),
  *                               nsamples calls folded into one
@@ -196,6 +198,14 @@ typedef struct vpt_params {
 } vpt_params;
 
 typedef struct vpt_scene vpt_scene; /* device-resident flattened scene */
+
+/* vpt_cuda_upload_scene_device_lights: timing of the device-side light construction */
+typedef struct vpt_lights_stats {
+  int32_t  num_lights;
+  uint64_t cdf_elements;  /* floats written */
+  float    weights_ms;    /* parallel pass: element areas / texel weights */
+  float    scan_ms;       /* running sums in the reference's (sequential) order */
+} vpt_lights_stats;
 typedef struct vpt_state vpt_state; /* device-resident accumulation image + rngs */
 
 /* per-call device statistics, filled by vpt_cuda_trace_samples */
@@ -222,6 +232,19 @@ int  vpt_cuda_host_register(void* ptr, size_t bytes);
 int  vpt_cuda_host_unregister(void* ptr);
 
 int  vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out);
+/* make_lights on the device (yocto_pathtrace.cpp:983-1049). desc->lights is
+ * ignored: the light list is enumerated from the description in the reference's order (emissive
+ * instances, environments, emissive sdfs) and every elements_cdf is built in HBM -- element areas
+ * / texel weights (max(rgba) * sin(theta), glibc-exact sinf) in parallel, then the running sums
+ * in the reference's sequential float order, so the CDFs equal make_lights' bit for bit.
+ * `stats` may be null. */
+int  vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** out,
+                                         vpt_lights_stats* stats);
+/* light `light` of an uploaded scene: ids = {instance, environment, sdf}; *num_elements floats of
+ * CDF are copied to `cdf` if it is non-null and `capacity` suffices */
+int  vpt_cuda_scene_num_lights(const vpt_scene* scene);
+int  vpt_cuda_download_light(const vpt_scene* scene, int light, int32_t ids[3], float* cdf,
+                             size_t capacity, int32_t* num_elements);
 void vpt_cuda_free_scene(vpt_scene* scene);
 size_t vpt_cuda_scene_bytes(const vpt_scene* scene);
 

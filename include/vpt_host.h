@@ -35,6 +35,12 @@ int  vpth_bvh_size(const vpth_scene* scene, int shape, int32_t* num_nodes, int32
 int  vpth_bvh_copy(const vpth_scene* scene, int shape, vpt_bvh_node* nodes, int32_t* prims);
 int  vpth_light_info(const vpth_scene* scene, int light, int32_t ids[3], int32_t* cdf_size);
 int  vpth_light_cdf(const vpth_scene* scene, int light, float* cdf);
+/* make_lights on the device (vpt_cuda_upload_scene_device_lights): (re)uploads the scene with the
+ * light list and CDFs built in HBM; renders created afterwards use it */
+int  vpth_scene_use_device_lights(vpth_scene* scene, vpt_lights_stats* stats);
+/* light `light` as it lies on the device (light < 0: *num_elements = number of lights) */
+int  vpth_device_light(vpth_scene* scene, int light, int32_t ids[3], float* cdf, size_t capacity,
+                       int32_t* num_elements);
 
 /* make_state; rngs_out (optional) receives the initial per-pixel generators */
 int  vpth_render_create(vpth_scene* scene, const vpt_params* params, vpth_render** out);

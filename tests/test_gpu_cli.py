@@ -57,6 +57,20 @@ def test_cli_png_and_batching(vpt, tmp_path):
     assert r.returncode == 0 and open(png, "rb").read(8) == b"\x89PNG\r\n\x1a\n"
 
 
+def test_cli_device_lights_changes_nothing(vpt, tmp_path):
+    """--device-lights: make_lights runs on the GPU; the render is the same image bit for bit."""
+    outs = []
+    for extra in ([], ["--device-lights"]):
+        out = str(tmp_path / f"l{len(extra)}.pfm")
+        r = subprocess.run([CLI, "--scene", util.scene_path("mixed"), "--output", out, "--shader",
+                            "volpathtrace", "--samples", "4", "--resolution", "64", "--bounces", "8",
+                            *extra], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert ("build lights (device)" in r.stdout) == bool(extra)
+        outs.append(read_pfm(out))
+    assert np.array_equal(outs[0], outs[1])
+
+
 def test_cli_rejects_what_the_reference_rejects(tmp_path):
     r = subprocess.run([CLI, "--scene", util.scene_path("mixed"), "--output", str(tmp_path / "x.pfm"),
                         "--shader", "nosuchshader"], capture_output=True, text=True)

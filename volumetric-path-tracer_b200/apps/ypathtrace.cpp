@@ -7,7 +7,8 @@
 // the scene is a ".vptscene" archive (asset loading stays with the reference's
 // loaders, see oracle/tools/vpt_export.cpp); --interactive is unavailable on
 // this box (no OpenGL); the image writers are .hdr / .pfm / .ppm / .png.
-// Added flags: --pipeline {auto,mega,wavefront}, --batch N, --device K.
+// Added flags: --pipeline {auto,mega,wavefront}, --batch N, --device K, --device-lights
+// (make_lights on the GPU).
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -146,13 +147,14 @@ int main(int argc, const char** argv) {
   auto outname     = std::string{"out.png"};
   auto interactive = false;
   auto device      = 0;
+  auto device_lights = false;
   auto params      = pathtrace_params{};
   params.batch     = 16;
   auto usage       = [&]() {
     printf("usage: ypathtrace [--scene S.vptscene] [--output IMG] [--interactive]\n"
            "  [--resolution 1..4096] [--shader NAME] [--samples 1..4096] [--bounces 1..128]\n"
            "  [--noparallel] [--noimplicitmis] [--stmaxiter 1..512]\n"
-           "  [--pipeline auto|mega|wavefront] [--batch N] [--device K]\n  shaders:");
+           "  [--pipeline auto|mega|wavefront] [--batch N] [--device K] [--device-lights]\n  shaders:");
     for (auto& n : pathtrace_shader_names) printf(" %s", n.c_str());
     printf("\n");
   };
@@ -178,6 +180,7 @@ int main(int argc, const char** argv) {
     else if (a == "--noimplicitmis") params.noimplicit_mis = true;
     else if (a == "--batch") params.batch = ranged("batch", next(), 1, 4096);
     else if (a == "--device") device = std::stoi(next());
+    else if (a == "--device-lights") device_lights = true;
     else if (a == "--shader") {
       auto name = next(), found = std::string{};
       for (size_t k = 0; k < pathtrace_shader_names.size(); k++)
@@ -213,9 +216,22 @@ int main(int argc, const char** argv) {
     auto bvh = make_bvh(scene, params);
     printf("build bvh: %.3f s\n", since(t0));
     t0          = clock();
-    auto lights = make_lights(scene, params);
-    printf("build lights: %.3f s\n", since(t0));
-    auto state = make_state(scene, params);
+    auto lights = pathtrace_lights{};
+    auto state  = pathtrace_state{};
+    if (device_lights) {
+      // make_lights on the device: the host object stays empty and only keys the cache
+      auto stats  = vpt_lights_stats{};
+      auto dscene = upload_scene_device_lights(scene, bvh, &stats);
+      printf("build lights (device): %.3f s (%d lights, %llu cdf entries: weights %.2f ms, "
+             "running sums %.2f ms)\n", since(t0), stats.num_lights,
+          (unsigned long long)stats.cdf_elements, stats.weights_ms, stats.scan_ms);
+      state = make_state(scene, params);
+      bind_device_scene(state, dscene, scene, bvh, lights);
+    } else {
+      lights = make_lights(scene, params);
+      printf("build lights: %.3f s\n", since(t0));
+      state = make_state(scene, params);
+    }
     t0         = clock();
     while (state.samples < params.samples) {
       pathtrace_samples(state, scene, bvh, lights, params);

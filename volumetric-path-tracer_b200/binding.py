@@ -48,6 +48,11 @@ class TraceStats(C.Structure):
                 ("top_kernel_units", C.c_uint64)]
 
 
+class LightsStats(C.Structure):
+    _fields_ = [("num_lights", C.c_int32), ("cdf_elements", C.c_uint64),
+                ("weights_ms", C.c_float), ("scan_ms", C.c_float)]
+
+
 BVH_NODE_DTYPE = np.dtype([("bbox_min", np.float32, 3), ("bbox_max", np.float32, 3),
                            ("start", np.int32), ("num", np.int16), ("axis", np.int8),
                            ("internal", np.uint8)])
@@ -158,6 +163,27 @@ class Scene:
             cdf = np.zeros(n.value, dtype=np.float32)
             if n.value:
                 _check(self._host.vpth_light_cdf(self._h, i, _fptr(cdf)))
+            out.append({"instance": ids[0], "environment": ids[1], "sdf": ids[2], "cdf": cdf})
+        return out
+
+    def use_device_lights(self) -> dict:
+        """make_lights on the device (SURVEY 8(f) #2); returns the construction timings."""
+        st = LightsStats()
+        _check(self._host.vpth_scene_use_device_lights(self._h, C.byref(st)))
+        return {"lights": st.num_lights, "cdf_elements": st.cdf_elements,
+                "weights_ms": st.weights_ms, "scan_ms": st.scan_ms}
+
+    def device_lights(self):
+        """The light list and CDFs as they lie in HBM."""
+        n = C.c_int32()
+        _check(self._host.vpth_device_light(self._h, -1, None, None, C.c_size_t(0), C.byref(n)))
+        out = []
+        for i in range(n.value):
+            ids, m = (C.c_int32 * 3)(), C.c_int32()
+            _check(self._host.vpth_device_light(self._h, i, ids, None, C.c_size_t(0), C.byref(m)))
+            cdf = np.zeros(m.value, dtype=np.float32)
+            if m.value:
+                _check(self._host.vpth_device_light(self._h, i, ids, _fptr(cdf), C.c_size_t(cdf.size), C.byref(m)))
             out.append({"instance": ids[0], "environment": ids[1], "sdf": ids[2], "cdf": cdf})
         return out
 

@@ -209,7 +209,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
       elems.push_back(q);
     }
     shapes.push_back({kind, pos_off, nrm_off, tex_off});
-    shapes.push_back({col_off, elem_off, 0, 0});
+    shapes.push_back({col_off, elem_off, nelem, 0});
 
     if (kind == kind_empty) continue;
     auto& bvh = in.shape_bvhs[s];
@@ -394,7 +394,11 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
       return fail(VPT_ERR_INVALID, "light " + std::to_string(l) + " references a missing object");
     lights.push_back({lt.instance, lt.environment, lt.sdf, (int)cdf.size()});
     lights.push_back({lt.num_elements, 0, 0, 0});
-    if (lt.num_elements > 0) cdf.insert(cdf.end(), lt.elements_cdf, lt.elements_cdf + lt.num_elements);
+    // a null pointer reserves the range: vpt_cuda_upload_scene_device_lights fills it on the device
+    if (lt.num_elements > 0 && lt.elements_cdf)
+      cdf.insert(cdf.end(), lt.elements_cdf, lt.elements_cdf + lt.num_elements);
+    else if (lt.num_elements > 0)
+      cdf.resize(cdf.size() + lt.num_elements, 0.0f);
   }
 
   // ---- sdf grids and functions -------------------------------------------------------

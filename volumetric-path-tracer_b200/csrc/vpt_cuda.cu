@@ -274,6 +274,176 @@ int vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out) {
   return VPT_OK;
 }
 
+// ---- make_lights on the device (yocto_pathtrace.cpp:983-1049) ------------------------------
+// weights: one thread per CDF entry
+__global__ void __launch_bounds__(256)
+    k_light_weights(const DScene sc, float* __restrict__ cdf, int light) {
+  auto l0 = ld4(sc.lights + 2 * light), l1 = ld4(sc.lights + 2 * light + 1);
+  int  n  = l1.x;
+  int  idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  float w = 0;
+  if (l0.x != invalidid) {
+    // element area in object space: triangle_area / quad_area (yocto_geometry.h:351-362)
+    auto in = ld4(sc.inst_frame + 4 * l0.x);
+    int  shape = f2i(in.w);
+    auto s0 = ld4(sc.shapes + 2 * shape), s1 = ld4(sc.shapes + 2 * shape + 1);
+    auto q  = ld4(sc.elems + s1.y + idx);
+    auto p0 = ld3(sc.vpos + 3 * (size_t)(s0.y + q.x)), p1 = ld3(sc.vpos + 3 * (size_t)(s0.y + q.y));
+    auto p2 = ld3(sc.vpos + 3 * (size_t)(s0.y + q.z));
+    if (s0.x == kind_triangles) {
+      w = length(cross(p1 - p0, p2 - p0)) / 2;
+    } else {
+      auto p3 = ld3(sc.vpos + 3 * (size_t)(s0.y + q.w));
+      w = length(cross(p1 - p0, p3 - p0)) / 2 + length(cross(p3 - p2, p1 - p2)) / 2;
+    }
+  } else if (l0.y != invalidid) {
+    // texel weight: max(rgba) * sin(theta) (yocto_pathtrace.cpp:1019-1027)
+    auto ev  = ld4(sc.environments + 9 * l0.y + 8);
+    auto tex = ld4(sc.textures + f2i(ev.w));
+    int  i = idx % tex.x, j = idx / tex.x;
+    auto th = (j + 0.5f) * pif / tex.y;
+    auto v  = lookup_texture(sc, tex, i, j, false);
+    w = vmax(vmax(vmax(v.x, v.y), v.z), v.w) * vsin(th);
+  }
+  cdf[l0.w + idx] = w;
+}
+// Running sums in index order, exactly the reference's float additions: the chain of dependent
+// FADDs cannot be split (float addition does not associate), so ONE thread per light walks it;
+// the other 255 threads of its block stage the values through shared memory in coalesced
+// tiles, which takes the DRAM / L2 latency off the chain (a lone thread reading HBM 16 bytes
+// at a time ran 34 ns per element; staged: the chain's own 4-cycle adds plus LDS).
+constexpr int scan_tile = 4096;
+__global__ void __launch_bounds__(256) k_light_scan(const DScene sc, float* __restrict__ cdf) {
+  __shared__ __align__(16) float tile[scan_tile];
+  int  light = blockIdx.x;
+  auto l0 = ld4(sc.lights + 2 * light), l1 = ld4(sc.lights + 2 * light + 1);
+  if (l0.z != invalidid) return;  // sdf lights hold one area, set by the host
+  float* c   = cdf + l0.w;
+  int    n   = l1.x;
+  float  acc = 0;  // thread 0 only
+  for (int base = 0; base < n; base += scan_tile) {
+    int m = n - base < scan_tile ? n - base : scan_tile;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) tile[i] = c[base + i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int i = 0;
+      if (base == 0) acc = tile[0], i = 1;  // elements_cdf[0] is the first weight itself
+      for (; i < m && (i & 15); i++) tile[i] = acc = acc + tile[i];
+      // 16 values per step through registers: 4 LDS.128, the 16 dependent adds, 4 STS.128
+      for (; i + 16 <= m; i += 16) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = *reinterpret_cast<const float4*>(tile + i + 4 * k);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          v[k].x = acc + v[k].x, v[k].y = v[k].x + v[k].y;
+          v[k].z = v[k].y + v[k].z, v[k].w = v[k].z + v[k].w;
+          acc = v[k].w;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) *reinterpret_cast<float4*>(tile + i + 4 * k) = v[k];
+      }
+      for (; i < m; i++) tile[i] = acc = acc + tile[i];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < m; i += blockDim.x) c[base + i] = tile[i];
+    __syncthreads();
+  }
+}
+
+int vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** out,
+    vpt_lights_stats* stats) {
+  if (!desc || !out) return set_error(VPT_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (auto r = require_device()) return r;
+  // the light list, in the reference's order; CDF ranges are reserved, not filled
+  auto is_zero3 = [](const float* v) { return v[0] == 0 && v[1] == 0 && v[2] == 0; };
+  std::vector<vpt_light_desc> lights;
+  std::vector<float>          sdf_area(desc->num_sdfs > 0 ? desc->num_sdfs : 0);
+  for (int i = 0; i < desc->num_instances; i++) {
+    auto& inst = desc->instances[i];
+    if (inst.material < 0 || inst.material >= desc->num_materials || inst.shape < 0 ||
+        inst.shape >= desc->num_shapes)
+      return set_error(VPT_ERR_INVALID, "instance references a missing shape/material");
+    if (is_zero3(desc->materials[inst.material].emission)) continue;
+    auto& sh = desc->shapes[inst.shape];
+    if (sh.num_triangles <= 0 && sh.num_quads <= 0) continue;
+    if (sh.num_triangles > 0 && sh.num_quads > 0)
+      return set_error(VPT_ERR_UNSUPPORTED,
+          "emissive shape with both triangles and quads: build its lights on the host");
+    lights.push_back({i, -1, -1, nullptr, sh.num_triangles > 0 ? sh.num_triangles : sh.num_quads});
+  }
+  for (int e = 0; e < desc->num_environments; e++) {
+    auto& ev = desc->environments[e];
+    if (is_zero3(ev.emission)) continue;
+    int n = 0;
+    if (ev.emission_tex >= 0) {
+      if (ev.emission_tex >= desc->num_textures)
+        return set_error(VPT_ERR_INVALID, "environment references a missing texture");
+      n = desc->textures[ev.emission_tex].width * desc->textures[ev.emission_tex].height;
+    }
+    lights.push_back({-1, e, -1, nullptr, n});
+  }
+  for (int s = 0; s < desc->num_sdfs; s++) {
+    auto& sd = desc->sdfs[s];
+    if (sd.material < 0 || sd.material >= desc->num_materials)
+      return set_error(VPT_ERR_INVALID, "sdf references a missing material");
+    if (is_zero3(desc->materials[sd.material].emission)) continue;
+    sdf_area[s] = sd.whd[0] * sd.whd[1];  // flat xy box assumed (yocto_pathtrace.cpp:1044)
+    lights.push_back({-1, -1, s, &sdf_area[s], 1});
+  }
+  auto with_lights       = *desc;
+  with_lights.num_lights = (int)lights.size();
+  with_lights.lights     = lights.data();
+  auto r = vpt_cuda_upload_scene(&with_lights, out);
+  if (r != VPT_OK) return r;
+  auto&       sc  = (*out)->flat.d;
+  auto        cdf = const_cast<float*>(sc.cdf);
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0), cudaEventCreate(&e1), cudaEventCreate(&e2);
+  uint64_t total = 0;
+  cudaEventRecord(e0);
+  for (int l = 0; l < (int)lights.size(); l++) {
+    if (lights[l].sdf >= 0 || lights[l].num_elements <= 0) continue;
+    total += lights[l].num_elements;
+    k_light_weights<<<(lights[l].num_elements + 255) / 256, 256>>>(sc, cdf, l);
+  }
+  cudaEventRecord(e1);
+  if (!lights.empty()) k_light_scan<<<(int)lights.size(), 256>>>(sc, cdf);
+  cudaEventRecord(e2);
+  auto e = cudaEventSynchronize(e2);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  float w_ms = 0, s_ms = 0;
+  cudaEventElapsedTime(&w_ms, e0, e1), cudaEventElapsedTime(&s_ms, e1, e2);
+  cudaEventDestroy(e0), cudaEventDestroy(e1), cudaEventDestroy(e2);
+  if (e != cudaSuccess) {
+    vpt_cuda_free_scene(*out);
+    *out = nullptr;
+    return cuda_fail(e, "device make_lights");
+  }
+  if (stats) *stats = {(int32_t)lights.size(), total, w_ms, s_ms};
+  return VPT_OK;
+}
+
+int vpt_cuda_scene_num_lights(const vpt_scene* scene) { return scene ? scene->flat.d.num_lights : 0; }
+
+int vpt_cuda_download_light(const vpt_scene* scene, int light, int32_t ids[3], float* cdf,
+    size_t capacity, int32_t* num_elements) {
+  if (!scene || !ids || !num_elements || light < 0 || light >= scene->flat.d.num_lights)
+    return set_error(VPT_ERR_INVALID, "bad light index");
+  i4 rec[2];
+  VPT_CUDA_TRY(cudaMemcpy(rec, scene->flat.d.lights + 2 * light, sizeof(rec), cudaMemcpyDeviceToHost));
+  ids[0] = rec[0].x, ids[1] = rec[0].y, ids[2] = rec[0].z;
+  *num_elements = rec[1].x;
+  if (cdf && rec[1].x > 0) {
+    if (capacity < (size_t)rec[1].x) return set_error(VPT_ERR_INVALID, "cdf buffer too small");
+    VPT_CUDA_TRY(cudaMemcpy(cdf, scene->flat.d.cdf + rec[0].w, sizeof(float) * rec[1].x,
+        cudaMemcpyDeviceToHost));
+  }
+  return VPT_OK;
+}
+
 void vpt_cuda_free_scene(vpt_scene* scene) {
   if (!scene) return;
   scene->flat.pool.release();

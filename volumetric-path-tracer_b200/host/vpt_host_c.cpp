@@ -149,6 +149,27 @@ int vpth_light_cdf(const vpth_scene* s, int light, float* cdf) {
   return VPT_OK;
 }
 
+int vpth_scene_use_device_lights(vpth_scene* s, vpt_lights_stats* stats) {
+  if (!s) return VPT_ERR_INVALID;
+  return guarded([&] { s->device = upload_scene_device_lights(s->scene, s->bvh, stats); });
+}
+
+int vpth_device_light(vpth_scene* s, int light, int32_t ids[3], float* cdf, size_t capacity,
+    int32_t* num_elements) {
+  if (!s) return VPT_ERR_INVALID;
+  vpt_scene* dev = nullptr;
+  auto r = guarded([&] { dev = device_scene_of(s); });
+  if (r != VPT_OK) return r;
+  if (light < 0) {  // query: number of lights on the device
+    if (!num_elements) return VPT_ERR_INVALID;
+    *num_elements = vpt_cuda_scene_num_lights(dev);
+    return VPT_OK;
+  }
+  r = vpt_cuda_download_light(dev, light, ids, cdf, capacity, num_elements);
+  if (r != VPT_OK) g_error = vpt_cuda_last_error();
+  return r;
+}
+
 int vpth_render_create(vpth_scene* scene, const vpt_params* params, vpth_render** out) {
   if (!scene || !params || !out) {
     g_error = "null argument";

@@ -273,6 +273,18 @@ static vpt_scene* upload_scene_raw(
   return out;
 }
 
+// make_lights on the device: the light list and CDFs are built in HBM by
+// vpt_cuda_upload_scene_device_lights (bit-identical to make_lights above)
+std::shared_ptr<device_scene> upload_scene_device_lights(
+    const scene_data& scene, const bvh_scene& bvh, vpt_lights_stats* stats) {
+  auto storage = scene_desc_storage{};
+  make_scene_desc(storage, scene, bvh, pathtrace_lights{});
+  auto dev = std::make_shared<device_scene>();
+  check(vpt_cuda_upload_scene_device_lights(&storage.desc, &dev->handle, stats),
+      "vpt_cuda_upload_scene_device_lights");
+  return dev;
+}
+
 std::shared_ptr<device_scene> upload_scene(
     const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights) {
   auto dev    = std::make_shared<device_scene>();

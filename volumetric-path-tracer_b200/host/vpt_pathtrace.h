@@ -145,6 +145,10 @@ void make_scene_desc(scene_desc_storage& storage, const scene_data& scene, const
 // Explicit device-scene management, for callers that render the same scene
 // from several states (the first pathtrace_samples call otherwise uploads).
 struct device_scene;
+// the same with make_lights run on the device; `lights` passed to later
+// pathtrace_samples calls is then only the cache key
+std::shared_ptr<device_scene> upload_scene_device_lights(
+    const scene_data& scene, const bvh_scene& bvh, vpt_lights_stats* stats = nullptr);
 std::shared_ptr<device_scene> upload_scene(
     const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
 void bind_device_scene(pathtrace_state& state, const std::shared_ptr<device_scene>& dscene,
