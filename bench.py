@@ -256,6 +256,11 @@ def gpu_arm(args, wl, rank, world, local_rank):
     r.reset(rng_offset)
     for _ in range(args.warmup):
         r.trace(spp)
+    if dist is not None:
+        # warm-up of the one collective too (NCCL sets up its channels on first use)
+        scratch = torch.zeros(r.height * r.width * 4, dtype=torch.float32, device="cuda")
+        pkg.sharding.reduce_images(scratch, dst=0)
+        del scratch
 
     # ---- device-resident timed region ------------------------------------------------------
     barrier()
