@@ -116,6 +116,24 @@ def test_first_hits_on_host_match_golden(vpt, hostsim, tmp_path, scene):
         assert ref["hits.ids"][:, 0].sum() > 1000
 
 
+def test_instance_culling_never_hides_a_hit(vpt, hostsim, tmp_path):
+    """bvh.cuh skips an instance whose enlarged world box the ray misses (the reference transforms
+    the ray and tests the root box in object space). `--cull-check` walks every culled instance the
+    way the reference would: none of them may hold a hit. The render must also stay the golden."""
+    import re
+    scene, shader, spp, res, bounces = "mixed", "volpathtrace", 2, 64, 8
+    out = str(tmp_path / "h.vptarch")
+    r = subprocess.run([hostsim, util.scene_path(scene), out, "--shader", shader, "--samples", str(spp),
+                        "--resolution", str(res), "--bounces", str(bounces), "--cull-check"],
+                       check=True, capture_output=True, text=True)
+    m = re.search(r"cull check: (\d+) instances culled, (\d+) of them", r.stdout)
+    assert m, r.stdout
+    assert int(m.group(1)) > 1000 and int(m.group(2)) == 0, r.stdout
+    got, ref = vpt.archive.load(out), golden(vpt, scene, shader, spp, res, bounces)
+    assert not util.bit_mismatch(got["image_sum"], ref["image_sum"]).any()
+    assert np.array_equal(got["rngs_after"], ref["rngs_after"])
+
+
 # ---- host structures -----------------------------------------------------------------------------
 def test_host_bvh_is_the_reference_bvh(vpt):
     """make_bvh (host/vpt_bvh.cpp) vs yocto's make_bvh: nodes byte for byte, primitive order equal."""
