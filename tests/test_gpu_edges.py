@@ -104,3 +104,32 @@ def test_state_reset_restarts_the_streams(vpt):
     assert not util.bit_mismatch(first, r.image(normalized=False)).any()
     r.close()
     sc.close()
+
+
+@pytest.mark.parametrize("env", [{"VPT_WF_PIPES": "1"}, {"VPT_WF_PIPES": "3"}, {"VPT_WF_PIPES": "4"},
+                                 {"VPT_WF_DRAIN": "0"}, {"VPT_WF_NO_PERSISTENT": "1"}],
+                         ids=lambda e: "-".join(f"{k}={v}" for k, v in e.items()))
+def test_wavefront_scheduling_never_changes_the_image(vpt, monkeypatch, env):
+    """Pipes, drain hand-over and the persistent extend only reschedule work: whatever the setting,
+    the image sums and generator states stay the reference's (yocto_pathtrace.cpp:1052-1092)."""
+    ref = util.oracle_render(vpt, "mixed", "volpathtrace", 2, 64, bounces=8)
+    assert ref is not None
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    img, rng = render(vpt, util.scene_path("mixed"), shader="volpathtrace", samples=2, resolution=64,
+                      bounces=8, pipeline="wavefront")
+    assert not util.bit_mismatch(img, ref["image_sum"]).any()
+    assert np.array_equal(rng, ref["rngs_after"])
+
+
+@pytest.mark.parametrize("suspend", ["0", "8", "32"])
+def test_parked_rays_never_change_the_image(vpt, monkeypatch, suspend):
+    """Sphere-tracing warps park their unfinished rays for the next launch (wavefront.cuh); the march
+    itself is unchanged, so any threshold gives the reference's image (yocto_pathtrace.cpp:289-307)."""
+    ref = util.oracle_render(vpt, "sdf_small", "implicit", 2, 64, bounces=4)
+    assert ref is not None
+    monkeypatch.setenv("VPT_WF_SUSPEND", suspend)
+    img, rng = render(vpt, util.scene_path("sdf_small"), shader="implicit", samples=2, resolution=64,
+                      bounces=4, pipeline="wavefront")
+    assert not util.bit_mismatch(img, ref["image_sum"]).any()
+    assert np.array_equal(rng, ref["rngs_after"])

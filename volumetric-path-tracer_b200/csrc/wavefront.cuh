@@ -27,6 +27,15 @@
 // lanes and 15 warps stalled on instruction fetch per issue before sorting).
 // The order inside a class is arbitrary; pixels do not interact, so results
 // are unaffected.
+//
+// Scheduling (none of it changes a pixel's sequence of operations):
+//   * pipes: mesh shaders run two independent wavefronts over interleaved
+//     tiles on two streams (wf_pipe), so that the latency-bound kernels of one
+//     fill the issue slots the other's draining extend leaves idle;
+//   * parked rays: a sphere-tracing warp that only drains hands its unfinished
+//     rays to the next iteration's launch (wf_bit_susp), see below;
+//   * the host looks at the counters every wf_batch iterations, two batches in
+//     flight per pipe, and hands the last slots to k_wf_drain.
 #pragma once
 
 #include <cstdio>
@@ -791,7 +800,7 @@ __global__ void __launch_bounds__(wf_block)
 // active slots at or below which the wavefront hands over to k_wf_drain;
 // VPT_WF_DRAIN overrides (0 disables), for experiments and the parity tests
 inline int wf_drain_threshold(int slots) {
-  static const char* env = getenv("VPT_WF_DRAIN");
+  const char* env = getenv("VPT_WF_DRAIN");
   if (env) return atoi(env);
   int t = slots / 8;
   return t < 32768 ? t : 32768;
@@ -882,7 +891,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     if (resident <= 0) persistent = false;
   }
   // lanes still walking at or below which a warp parks its rays once the queue is empty
-  static const char* susp_env = getenv("VPT_WF_SUSPEND");
+  const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
   if (persistent) {
     e = wf.reserve_suspended(resident * wf_block, wf_susp_record_f4(scene.stack_depth));
