@@ -230,8 +230,15 @@ struct trav_t {
   VPT_FN int descend(const DScene& sc, const ray3& ray, stack_t st) {
     int leaf = 0, enter = -1;
     int pops = trav_pops;
-    while (cur != 0 && leaf == 0 && enter < 0 && pops != 0) {
+    VPT_WORK(rounds, 1);
+    // The ray (o, d, dinv, plain, kind) is invariant inside the pop loop: leaving an instance
+    // (sentinel) ends it and is handled outside, so the loop carries only the stack state
+    // (with the restore inside it, ptxas moved ~20 registers of ray state around every pop).
+    bool again = true;
+    while (again) {
+    while (cur != 0 && leaf == 0 && enter == -1 && pops != 0) {
       pops--;
+      VPT_WORK(pops, 1);
       auto  en = st.get(--cur);
       int   e  = en.ref;
       float te = en.t0;
@@ -257,14 +264,23 @@ struct trav_t {
         int x = ~e, tag = x & 3;
         if (tag == ref_leaf) {
           if (te <= tmax * box_slack) leaf = x >> 2;
+          else VPT_WORK(stale_pops, 1);
+          VPT_WORK(leaf_pops, 1);
         } else if (tag == ref_instance) {
           enter = x >> 2;
         } else {
-          o = ray.o, d = ray.d;
-          dinv = wdinv, plain = wplain;
-          kind = -1;
+          enter = -2;
         }
       }
+    }
+    again = false;
+    if (enter == -2) {  // back to the world-space ray
+      o = ray.o, d = ray.d;
+      dinv = wdinv, plain = wplain;
+      kind = -1;
+      enter = -1;
+      again = cur != 0 && pops != 0;
+    }
     }
     if (enter >= 0) {
       // transform the ray, test the shape's root box (yocto_bvh.cpp:854-858, :714-722)
