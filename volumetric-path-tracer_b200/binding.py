@@ -244,7 +244,7 @@ class Render:
         return self._host.vpth_render_done_samples(self._h)
 
     def image(self, normalized: bool = True) -> np.ndarray:
-        out = np.zeros((self.height, self.width, 4), dtype=np.float32)
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
         _check(self._host.vpth_render_get_image(self._h, _fptr(out), int(normalized)))
         return out
 

@@ -212,15 +212,19 @@ int vpth_render_get_rngs(vpth_render* r, uint64_t* rngs) {
 int vpth_render_reset(vpth_render* r, uint64_t rng_offset) {
   if (!r) return VPT_ERR_INVALID;
   return guarded([&] {
-    r->state.rngs    = r->initial_rngs;
     r->state.samples = 0;
-    r->state.image.assign(r->state.image.size(), {0, 0, 0, 0});
     if (auto dstate = device_handle(r->state)) {
-      if (vpt_cuda_reset_state(dstate, (const uint64_t*)r->state.rngs.data()) != VPT_OK)
+      // straight from the pinned initial generators; the host mirrors are refreshed lazily
+      if (vpt_cuda_reset_state(dstate, (const uint64_t*)r->initial_rngs.data()) != VPT_OK)
         throw std::runtime_error(vpt_cuda_last_error());
       if (rng_offset && vpt_cuda_advance_rngs(dstate, rng_offset) != VPT_OK)
         throw std::runtime_error(vpt_cuda_last_error());
-    } else if (rng_offset) {
+      mark_host_stale(r->state);
+      return;
+    }
+    r->state.rngs = r->initial_rngs;
+    r->state.image.assign(r->state.image.size(), {0, 0, 0, 0});
+    if (rng_offset) {
       // no device state yet: jump the host copies (same O(log n) recurrence)
       for (auto& g : r->state.rngs) {
         uint64_t cur_mult = 6364136223846793005ULL, cur_plus = g.inc, acc_mult = 1, acc_plus = 0;
@@ -257,7 +261,7 @@ int vpth_render_get_image(vpth_render* r, float* rgba, int normalized) {
       auto img = get_render(r->state);
       memcpy(rgba, img.pixels.data(), n * sizeof(vec4f));
     } else {
-      sync_state(r->state);
+      sync_image(r->state);
       memcpy(rgba, r->state.image.data(), n * sizeof(vec4f));
     }
   });

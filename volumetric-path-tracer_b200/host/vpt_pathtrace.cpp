@@ -147,6 +147,7 @@ struct device_binding {
   const void* bvh_key   = nullptr;
   const void* light_key = nullptr;
   bool        dirty     = false;  // device image is ahead of state.image
+  bool        dirty_rngs = false; // device generators are ahead of state.rngs
   ~device_binding() {
     if (state) vpt_cuda_free_state(state);
   }
@@ -349,18 +350,30 @@ void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bv
   check(vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams, params.batch > 0 ? params.batch : 1),
       "vpt_cuda_trace_samples");
   state.samples = vpt_cuda_state_samples(dev.state);
-  dev.dirty     = true;
+  dev.dirty = dev.dirty_rngs = true;
 }
 
-void sync_state(pathtrace_state& state) {
+// the accumulation image only (what get_render needs): half the bytes of sync_state
+void sync_image(pathtrace_state& state) {
   if (!state.device || !state.device->state || !state.device->dirty) return;
   auto& dev = *state.device;
   check(vpt_cuda_download_image(dev.state, (float*)state.image.data(), state.image.size() * 4),
       "vpt_cuda_download_image");
-  check(vpt_cuda_download_rngs(dev.state, (uint64_t*)state.rngs.data(), state.rngs.size() * 2),
-      "vpt_cuda_download_rngs");
   state.hits.assign(state.hits.size(), state.samples);
   dev.dirty = false;
+}
+
+void sync_state(pathtrace_state& state) {
+  sync_image(state);
+  if (!state.device || !state.device->state || !state.device->dirty_rngs) return;
+  auto& dev = *state.device;
+  check(vpt_cuda_download_rngs(dev.state, (uint64_t*)state.rngs.data(), state.rngs.size() * 2),
+      "vpt_cuda_download_rngs");
+  dev.dirty_rngs = false;
+}
+
+void mark_host_stale(pathtrace_state& state) {
+  if (state.device) state.device->dirty = state.device->dirty_rngs = true;
 }
 
 std::vector<uint8_t> get_render_srgb8(pathtrace_state& state) {
@@ -385,7 +398,7 @@ void get_render(color_image& image, const pathtrace_state& state) {
     throw std::invalid_argument{"image should have the same size"};
   if (!image.linear) throw std::invalid_argument{"expected linear image"};
   // refresh the host mirror; the reference API takes the state by const ref
-  sync_state(const_cast<pathtrace_state&>(state));
+  sync_image(const_cast<pathtrace_state&>(state));
   auto scale = 1.0f / (float)state.samples;
   for (size_t idx = 0; idx < (size_t)state.width * state.height; idx++)
     image.pixels[idx] = state.image[idx] * scale;

@@ -114,6 +114,8 @@ inline void trace_samples(pathtrace_state& state, const scene_data& scene, const
 
 // Copies the device accumulation image and generators back into `state`.
 void sync_state(pathtrace_state& state);
+// the same for state.image / state.hits only (get_render uses it)
+void sync_image(pathtrace_state& state);
 
 // Get resulting render (divides by state.samples, yocto_pathtrace.cpp:1105-1116);
 // the second form throws std::invalid_argument on a size / linearity mismatch.
@@ -158,6 +160,9 @@ vpt_state* device_handle(pathtrace_state& state);
 // the device image was replaced (e.g. by a cross-GPU reduce): state.samples becomes
 // `samples` and the host mirror is refreshed on the next sync_state / get_render
 void mark_device_dirty(pathtrace_state& state, int samples);
+// the device state was re-initialised behind the host mirrors' back (reset): image and
+// generators are downloaded again on the next sync
+void mark_host_stale(pathtrace_state& state);
 
 // Device statistics of the last pathtrace_samples call on this state.
 vpt_trace_stats get_trace_stats(const pathtrace_state& state);
