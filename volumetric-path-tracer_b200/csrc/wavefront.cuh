@@ -893,10 +893,13 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   // lanes still walking at or below which a warp parks its rays once the queue is empty
   const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
-  if (persistent) {
+  // parked BVH walks need record pools (sphere tracing parks into the slot record itself)
+#if defined(VPT_WF_SUSPEND_MESH)
+  if (persistent && !is_sdf_shader<S>()) {
     e = wf.reserve_suspended(resident * wf_block, wf_susp_record_f4(scene.stack_depth));
     if (e != cudaSuccess) return e;
   }
+#endif
   *launches = 0;
   // the first extend launch of every batch of pipe 0 is timed with CUDA events: its ray count
   // is known exactly, so the pairs give the dominant kernel's rays per second (with two
