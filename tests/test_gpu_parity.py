@@ -191,18 +191,26 @@ def test_cameras_bit_exact(vpt, scenes, camera, shader):
     r.close()
 
 
-def test_full_size_render_is_bit_exact(vpt, scenes):
-    """BASELINE.json's headline configuration at its full size (03_volume, volpathtrace,
-    1280x533, 64 bounces) for as many samples as the oracle renders in a few seconds."""
-    sc = scenes("03_volume")
-    spp = 4
-    ref = util.oracle_render(vpt, "03_volume", "volpathtrace", spp, 1280, bounces=64)
+@pytest.mark.parametrize("scene,shader,res,bounces,spp,size", [
+    ("03_volume", "volpathtrace", 1280, 64, 4, (1280, 533)),
+    ("01_surface", "pathtrace", 720, 4, 2, (720, 300)),
+    ("05_head1ss", "volpathtrace", 1280, 64, 2, (1280, 1280)),
+    ("06_gridsdf", "implicit", 1280, 4, 2, (1280, 533)),
+    ("07_sdfunction", "implicit", 1920, 4, 2, (1920, 800))])
+def test_full_size_render_is_bit_exact(vpt, scenes, scene, shader, res, bounces, spp, size):
+    """Every BASELINE.json configuration at the size bench.py runs it (03_volume is the headline:
+    volpathtrace, 1280x533, 64 bounces), for as many samples as the oracle renders in a few seconds:
+    image sums and generator states equal the reference CPU path's bit for bit."""
+    if util.scene_path(scene) is None:
+        pytest.skip(f"{scene}.vptscene not built")
+    sc = scenes(scene)
+    ref = util.oracle_render(vpt, scene, shader, spp, res, bounces=bounces)
     if ref is None:
         pytest.skip("oracle binary absent")
-    r = vpt.binding.Render(sc, vpt.binding.make_params(shader="volpathtrace", samples=spp,
-                                                       resolution=1280, bounces=64))
+    r = vpt.binding.Render(sc, vpt.binding.make_params(shader=shader, samples=spp, resolution=res,
+                                                       bounces=bounces))
     r.trace(spp)
-    assert (r.width, r.height) == (1280, 533)
+    assert (r.width, r.height) == size
     assert not util.bit_mismatch(r.image(normalized=False), ref["image_sum"]).any()
     assert np.array_equal(r.rngs(), ref["rngs_after"])
     r.close()
