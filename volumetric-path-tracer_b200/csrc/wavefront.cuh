@@ -472,12 +472,16 @@ __global__ void __launch_bounds__(wf_block)
 #if !defined(VPT_EXT_BLOCKS)
 #define VPT_EXT_BLOCKS 6
 #endif
-constexpr int wf_refill    = VPT_WF_REFILL;
+constexpr int wf_refill    = VPT_WF_REFILL;  // BVH walks
+constexpr int wf_refill_sdf = 4;             // sphere tracing (B200: 07_sdfunction 147.6 -> 143.9 ms per 16 spp)
 #if !defined(VPT_WF_SUSPEND_AT)
 #define VPT_WF_SUSPEND_AT 20
 #endif
 constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in place)
-constexpr int wf_sdf_steps = 4;
+#if !defined(VPT_WF_SDF_STEPS)
+#define VPT_WF_SDF_STEPS 4
+#endif
+constexpr int wf_sdf_steps = VPT_WF_SDF_STEPS;
 
 template <int S>
 __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
@@ -517,7 +521,7 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
   sp.finished = true;
   while (running) {
     unsigned idle = __ballot_sync(full, !has_ray);
-    if (more && (__popc(idle) >= wf_refill)) {
+    if (more && (__popc(idle) >= (sdf ? wf_refill_sdf : wf_refill))) {
       int base = 0;
       if (lane == 0) base = atomicAdd(&w.counters->ext_head, __popc(idle));
       base = __shfl_sync(full, base, 0);
