@@ -60,6 +60,8 @@ def main(argv):
     jobs = {
         "03_volume": build_03_volume,
         "01_surface": standins.build_01_surface,
+        "02_rollingteapot": standins.build_02_rollingteapot,
+        "04_head1": standins.build_04_head1,
         "05_head1ss": standins.build_05_head1ss,
         "06_gridsdf": standins.build_06_gridsdf,
         "07_sdfunction": standins.build_07_sdfunction,

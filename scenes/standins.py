@@ -51,6 +51,81 @@ def write_obj_quad_sphere(path, steps_u=64, steps_v=32, radius=0.075, center=(0,
         f.write("\n".join(lines) + "\n")
 
 
+def write_obj_lathe(path, profile, steps_u, center=(0, 0, 0), handle=None):
+    """Quad surface of revolution of `profile` [(radius, height), ...] (first and last radius 0:
+    pole fans of triangles), with texcoords; optionally a quad torus `handle` = (centre, major
+    radius, minor radius, steps) in the xy plane. The teapot stand-in."""
+    lines, faces = [], []
+    nv = len(profile)
+    for j, (r, y) in enumerate(profile):
+        for i in range(steps_u + 1):
+            ph = 2 * np.pi * i / steps_u
+            lines.append("v %.9g %.9g %.9g" % (center[0] + r * np.cos(ph), center[1] + y,
+                                              center[2] + r * np.sin(ph)))
+    vts = [(i / steps_u, 1 - j / (nv - 1)) for j in range(nv) for i in range(steps_u + 1)]
+    row = steps_u + 1
+    for j in range(nv - 1):
+        for i in range(steps_u):
+            a, b = j * row + i + 1, j * row + i + 2
+            c, d = (j + 1) * row + i + 2, (j + 1) * row + i + 1
+            if profile[j][0] == 0:
+                faces.append((a, c, d))
+            elif profile[j + 1][0] == 0:
+                faces.append((a, b, d))
+            else:
+                faces.append((a, b, c, d))
+    if handle is not None:
+        hc, major, minor, hs = handle
+        base = len(vts)
+        for j in range(hs + 1):
+            th = 2 * np.pi * j / hs
+            for i in range(hs + 1):
+                ph = 2 * np.pi * i / hs
+                rr = major + minor * np.cos(ph)
+                lines.append("v %.9g %.9g %.9g" % (center[0] + hc[0] + rr * np.cos(th),
+                                                  center[1] + hc[1] + rr * np.sin(th),
+                                                  center[2] + hc[2] + minor * np.sin(ph)))
+                vts.append((j / hs, i / hs))
+        for j in range(hs):
+            for i in range(hs):
+                a = base + j * (hs + 1) + i + 1
+                faces.append((a, a + 1, a + hs + 2, a + hs + 1))
+    lines += ["vt %.9g %.9g" % t for t in vts]
+    lines += ["f " + " ".join(f"{k}/{k}" for k in f) for f in faces]
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+
+
+TEAPOT_PROFILE = [(0.0, 0.0), (0.045, 0.0), (0.062, 0.012), (0.072, 0.035), (0.068, 0.060),
+                  (0.052, 0.080), (0.040, 0.088), (0.043, 0.092), (0.030, 0.100), (0.012, 0.106),
+                  (0.010, 0.114), (0.016, 0.120), (0.0, 0.126)]
+
+
+def refine_profile(profile, times):
+    """Midpoint refinement of a lathe profile (keeps the poles)."""
+    for _ in range(times):
+        out = []
+        for a, b in zip(profile[:-1], profile[1:]):
+            out += [a, ((a[0] + b[0]) / 2, (a[1] + b[1]) / 2)]
+        profile = out + [profile[-1]]
+    return profile
+
+
+def write_normal_png(path, size=1024):
+    """Tangent-space normal map (byte, linear): gradients of tiling value noise."""
+    from PIL import Image
+
+    rng = np.random.default_rng(SEED + 2)
+    h = sum(value_noise(size, 16 * 2 ** o, rng) / 2 ** o for o in range(3))
+    gx = (np.roll(h, -1, axis=1) - np.roll(h, 1, axis=1)) * size / 64.0
+    gy = (np.roll(h, -1, axis=0) - np.roll(h, 1, axis=0)) * size / 64.0
+    n = np.stack([-gx, -gy, np.ones_like(h)], 2)
+    n /= np.linalg.norm(n, axis=2, keepdims=True)
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    Image.fromarray(((n * 0.5 + 0.5) * 255 + 0.5).astype(np.uint8)).save(path)
+
+
 def icosphere(subdivisions):
     """Unit icosphere: (positions [n,3] float64, triangles [m,3] int32)."""
     t = (1 + 5 ** 0.5) / 2
@@ -250,6 +325,46 @@ def build_01_surface(force=False):
         if not os.path.exists(p):
             write_obj_quad_sphere(p)
     return export(d, "surface.json", "01_surface", force)
+
+
+def build_02_rollingteapot(force=False):
+    """tests/02_rollingteapot: the four teapot OBJs are missing; a lathe teapot with a torus
+    handle stands in (a dense one as the plain shape, a coarse cage for the Catmull-Clark
+    subdiv: `subdivisions 1, smooth`)."""
+    d = _work_dir("02_rollingteapot")
+    dense = os.path.join(d, "shapes", "rollingteapot-shape.obj")
+    if not os.path.exists(dense):
+        write_obj_lathe(dense, refine_profile(TEAPOT_PROFILE, 2), 96,
+                        handle=((0.088, 0.06, 0.0), 0.028, 0.006, 24))
+    for sub in ("shapes", "subdivs"):
+        cage = os.path.join(d, sub, "rollingteapot-subdiv.obj")
+        if not os.path.exists(cage):
+            write_obj_lathe(cage, TEAPOT_PROFILE, 24, handle=((0.088, 0.06, 0.0), 0.028, 0.007, 8))
+    return export(d, "rollingteapot.json", "02_rollingteapot", force)
+
+
+def build_04_head1(force=False, subdivisions=None):
+    """tests/04_head1: the 05 stand-in mesh, a noise colour texture and a noise normal map;
+    texture3.hdr (two environments share it) is shipped."""
+    d = _work_dir("04_head1")
+    cam = json.load(open(os.path.join(d, "head1.json")))["cameras"][0]
+    fr = np.array(cam["frame"], float).reshape(4, 3)
+    center = fr[3] - fr[2] * cam["focus"]
+    half = cam["focus"] * 0.036 / 2 / cam.get("lens", 0.05)
+    radius = 0.6 * half / 1.2
+    # 7 subdivisions (327 680 triangles): 04 is not a BASELINE configuration, and the snapshot
+    # that travels to the GPU box is capped at 512 MiB
+    subdivisions = subdivisions or int(os.environ.get("VPT_HEAD1_SUBDIV", "7"))
+    ply = os.path.join(d, "shapes", "shape1.ply")
+    if not os.path.exists(ply):
+        write_ply(ply, *displaced_head(subdivisions, center, radius))
+    png = os.path.join(d, "textures", "texture1.png")
+    if not os.path.exists(png):
+        write_noise_png(png, size=1024)
+    nrm = os.path.join(d, "textures", "texture2.png")
+    if not os.path.exists(nrm):
+        write_normal_png(nrm)
+    return export(d, "head1.json", "04_head1", force)
 
 
 def build_05_head1ss(force=False, subdivisions=None):

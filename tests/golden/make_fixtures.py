@@ -209,7 +209,8 @@ def build_mixed():
             material(MATTE, emission=(12, 11, 9), emission_tex=4),
             material(MATTE, color=(0.8, 0.8, 0.9), opacity=0.5),
             material(REFRACTIVE, color=(0.9, 1.0, 0.9), roughness=0.2, ior=1.33),
-            material(TRANSPARENT, color=(0.9, 0.9, 1.0), roughness=0.0)]
+            material(TRANSPARENT, color=(0.9, 0.9, 1.0), roughness=0.0),
+            material(MATTE, color=(0.2, 0.2, 0.2), emission=(5, 6, 8))]   # 13: triangle-mesh emitter
     a["materials.f"] = f32(np.stack([m[0] for m in mats]))
     a["materials.i"] = np.stack([m[1] for m in mats]).astype(np.int32)
 
@@ -225,11 +226,17 @@ def build_mixed():
             (frame((0.0, 1.6, 0.3), rot_x=np.pi, scale=(1.5, 1, 1.5)), 4, 9),   # area light
             (frame((-0.45, 0.2, 1.25), rot_x=np.pi / 2, scale=(0.6, 1, 0.6)), 4, 10),  # half-opaque card
             (frame((1.3, 0.2, 0.5)), 3, 11),
-            (frame((-1.3, 0.31, 0.5), rot_x=np.pi / 2), 5, 12)]
+            (frame((-1.3, 0.31, 0.5), rot_x=np.pi / 2), 5, 12),
+            # an emissive TRIANGLE mesh (facetted icosphere, non-rigid frame): sample_triangle
+            # in sample_lights and the triangle areas of make_lights
+            (frame((0.95, 0.95, 0.55), scale=(0.45, 0.3, 0.45), rot_y=0.3), 3, 13)]
     a["instances.frame"] = f32(np.stack([i[0] for i in inst]))
     a["instances.ids"] = np.asarray([[i[1], i[2]] for i in inst], np.int32)
-    a["environments.f"] = f32([np.concatenate([frame(rot_y=0.7), f32([0.8, 0.8, 0.8])])])
-    a["environments.i"] = np.asarray([[2]], np.int32)
+    # two environments (eval_environment sums them, yocto_scene.cpp:645-651); the second has
+    # no texture: uniform-sphere light sampling and the 1 / 4 pi pdf (yocto_pathtrace.cpp:343, :414)
+    a["environments.f"] = f32([np.concatenate([frame(rot_y=0.7), f32([0.8, 0.8, 0.8])]),
+                               np.concatenate([frame(rot_y=-0.3, rot_x=0.2), f32([0.12, 0.1, 0.08])])])
+    a["environments.i"] = np.asarray([[2], [-1]], np.int32)
     a["volumes.count"] = np.asarray([0], np.int32)
     a["vol_instances.f"] = np.zeros((0, 13), np.float32)
     a["vol_instances.i"] = np.zeros((0, 2), np.int32)
@@ -272,15 +279,48 @@ def build_sdf_small():
     def sdf(type_, mat, o, params=(0, 0, 0, 0), whd=(0, 0, 0), **kw):
         return np.concatenate([frame(o, **kw), f32(params), f32(whd)]), (type_, mat)
 
+    def sdf_at(type_, mat, world_center, whd, **kw):
+        """world -> local is the FORWARD frame in the reference (yocto_sdfs.cpp:20): pick the
+        frame origin so that the box [0, whd] sits around `world_center`."""
+        m = frame((0, 0, 0), **kw).astype(np.float64)[:9].reshape(3, 3).T  # columns x, y, z
+        o = np.asarray(whd, np.float64) / 2 - m @ np.asarray(world_center, np.float64)
+        return sdf(type_, mat, tuple(o), whd=whd, **kw)
+
     sdfs = [sdf(SDF_PLANE, 0, (0, 0.25, 0)),                       # world -> local uses the forward frame
             sdf(SDF_SPHERE, 1, (0.3, -1.4, -0.2), params=(0.25, 0, 0, 0)),
             sdf(SDF_TORUS, 3, (0.6, 0.05, -0.5), params=(0.25, 0.08, 0, 0)),
             sdf(SDF_BOX, 4, (0.2, 0.1, 0.3), whd=(0.3, 0.3, 0.3)),
             sdf(SDF_BBOX, 5, (-0.3, -0.1, 0.5), params=(0.02, 0.2, 0.15, 0.2)),
             sdf(SDF_CAPPED_CONE, 6, (-0.2, -0.05, -0.4), params=(0.2, 0.2, 0.05, 0)),
-            sdf(SDF_SPHERE, 2, (-0.9, -0.1, 0.2), params=(0.2, 0, 0, 0))]
+            sdf(SDF_SPHERE, 2, (-0.9, -0.1, 0.2), params=(0.2, 0, 0, 0)),
+            # an emissive box light with a rotated frame: the sdf branch of sample_lights
+            # (inverse(frame), yocto_pathtrace.cpp:327-332) and of sample_lights_pdf (:382-394)
+            sdf_at(SDF_BOX, 1, (-0.45, 0.75, 0.1), whd=(0.35, 0.25, 0.02), rot_y=0.5, rot_x=0.35)]
     a["sdfs.f"] = f32(np.stack([s[0] for s in sdfs]))
     a["sdfs.i"] = np.asarray([s[1] for s in sdfs], np.int32)
+    return a
+
+
+def build_dark():
+    """No emitter at all (no emissive material, no environment): the light list is empty.
+    The reference indexes an empty vector there (UB); the device ends the path (lights.cuh)."""
+    a = {"meta": np.asarray([1, 0, 0, 0], np.int32)}
+    a["cameras"] = f32(np.stack([camera((0.0, 1.0, 3.0), (0, 0.25, 0))]))
+    add_textures(a, [])
+    add_shapes(a, [quad_shape(2.0), icosphere(1, 0.4)])
+    mats = [material(MATTE, color=(0.8, 0.8, 0.8)), material(GLOSSY, color=(0.6, 0.3, 0.2), roughness=0.3)]
+    a["materials.f"] = f32(np.stack([m[0] for m in mats]))
+    a["materials.i"] = np.stack([m[1] for m in mats]).astype(np.int32)
+    inst = [(frame(), 0, 0), (frame((0, 0.4, 0)), 1, 1)]
+    a["instances.frame"] = f32(np.stack([i[0] for i in inst]))
+    a["instances.ids"] = np.asarray([[i[1], i[2]] for i in inst], np.int32)
+    a["environments.f"] = np.zeros((0, 15), np.float32)
+    a["environments.i"] = np.zeros((0, 1), np.int32)
+    a["volumes.count"] = np.asarray([0], np.int32)
+    a["vol_instances.f"] = np.zeros((0, 13), np.float32)
+    a["vol_instances.i"] = np.zeros((0, 2), np.int32)
+    a["sdfs.f"] = np.zeros((0, 19), np.float32)
+    a["sdfs.i"] = np.zeros((0, 2), np.int32)
     return a
 
 
@@ -291,7 +331,8 @@ def main():
     vpt = entry.load_package()
     vpt.archive.save(os.path.join(HERE, "mixed.vptscene"), build_mixed())
     vpt.archive.save(os.path.join(HERE, "sdf_small.vptscene"), build_sdf_small())
-    print("wrote mixed.vptscene, sdf_small.vptscene")
+    vpt.archive.save(os.path.join(HERE, "dark.vptscene"), build_dark())
+    print("wrote mixed.vptscene, sdf_small.vptscene, dark.vptscene")
     if "--scenes" in sys.argv:
         return
     if not util.have_ref():

@@ -246,8 +246,10 @@ int main(int argc, const char** argv) {
       printf(" iq_box_tests=%.3f iq_tri_tests=%.3f node_visits=%.3f cull_tests=%.3f\n",
           g_work.iq_box_tests / paths, g_work.iq_tri_tests / paths, g_work.node_visits / paths,
           g_work.cull_tests / paths);
-      printf("hostsim traversal per path: rounds=%.2f pops=%.2f leaf_pops=%.2f stale_leaf_pops=%.2f\n",
-          g_work.rounds / paths, g_work.pops / paths, g_work.leaf_pops / paths, g_work.stale_pops / paths);
+      printf("hostsim traversal per path: rounds=%.2f pops=%.2f leaf_pops=%.2f stale_leaf_pops=%.2f "
+             "wide_visits=%.2f wide_slot_tests=%.2f stale_node_pops=%.2f\n",
+          g_work.rounds / paths, g_work.pops / paths, g_work.leaf_pops / paths, g_work.stale_pops / paths,
+          g_work.wide_visits / paths, g_work.wide_slot_tests / paths, g_work.stale_node_pops / paths);
       if (vpt_cull_check_on)
         printf("hostsim: cull check: %lld instances culled, %lld of them hold a hit the reference "
                "would find\n", (long long)g_work.culled, (long long)g_work.cull_wrong);

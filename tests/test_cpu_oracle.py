@@ -152,7 +152,10 @@ def test_lights_and_cdfs_match_reference(vpt):
     ref = vpt.archive.load(os.path.join(util.GOLDEN, "mixed_host.vptarch"))
     sc = vpt.binding.Scene(util.scene_path("mixed"))
     lights = sc.lights()
-    assert len(lights) == ref["lights.ids"].shape[0] == 2
+    # quad area light, TRIANGLE-mesh emitter (80 triangle areas), textured environment (texel
+    # weights), texture-less environment (empty CDF)
+    assert len(lights) == ref["lights.ids"].shape[0] == 4
+    assert [len(l["cdf"]) for l in lights] == [1, 80, 32 * 16, 0]
     for i, l in enumerate(lights):
         assert [l["instance"], l["environment"], l["sdf"]][:2] == list(ref["lights.ids"][i][:2])
         assert not (l["cdf"].view(np.uint32) != ref[f"lights.cdf{i}"].view(np.uint32)).any()

@@ -57,6 +57,34 @@ def test_one_bounce_and_many_bounces_bit_exact(vpt):
         assert np.array_equal(rng, ref["rngs_after"])
 
 
+@pytest.mark.parametrize("shader", ["pathtrace", "volpathtrace", "naive", "eyelight"])
+@pytest.mark.parametrize("pipeline", ["mega", "wavefront"])
+def test_scene_without_emitters_renders_black(vpt, shader, pipeline):
+    """No emissive material and no environment: the light list is empty. The reference indexes
+    an empty vector there (undefined behaviour on the host); the device must not read out of
+    bounds: light sampling yields a zero direction, which ends the path (lights.cuh), so the
+    lit shaders render black with alpha = 1 on geometry, and the context stays usable."""
+    path = util.scene_path("dark")
+    img, _ = render(vpt, path, shader=shader, samples=4, resolution=96, pipeline=pipeline)
+    assert np.isfinite(img).all()
+    assert (img[..., :3] == 0).all()
+    assert img[..., 3].max() == 4 and img[..., 3].min() == 0
+    # the device is still healthy: a normal render right after
+    img2, _ = render(vpt, util.scene_path("mixed"), shader="color", samples=1, resolution=64)
+    assert img2[..., :3].max() > 0
+
+
+def test_bounces_outside_the_packed_range_are_rejected(vpt):
+    sc = vpt.binding.Scene(util.scene_path("mixed"))
+    for bounces in (0, 65536):
+        r = vpt.binding.Render(sc, vpt.binding.make_params(shader="pathtrace", samples=1,
+                                                           resolution=32, bounces=bounces))
+        with pytest.raises(Exception, match="bounces"):
+            r.trace(1)
+        r.close()
+    sc.close()
+
+
 def test_point_and_line_primitives_are_rejected(vpt, tmp_path):
     """The device path supports triangles and quads (all the reference's scenes); anything else
     fails at upload with VPT_ERR_UNSUPPORTED instead of rendering something different."""

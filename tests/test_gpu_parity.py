@@ -18,7 +18,7 @@ import util
 
 pytestmark = pytest.mark.gpu
 
-MESH_SCENES = ["03_volume", "01_surface", "mixed"]
+MESH_SCENES = ["03_volume", "01_surface", "mixed", "02_rollingteapot", "04_head1"]
 SDF_SCENES = ["07_sdfunction", "06_gridsdf", "sdf_small"]
 
 
@@ -116,6 +116,7 @@ def test_implicit_normal_bit_exact(vpt, scenes, scene):
 
 STOCHASTIC = [("03_volume", "volpathtrace", 64), ("03_volume", "pathtrace", 4),
               ("03_volume", "naive", 4), ("01_surface", "pathtrace", 4),
+              ("02_rollingteapot", "pathtrace", 4), ("04_head1", "volpathtrace", 4),
               ("mixed", "pathtrace", 8), ("mixed", "volpathtrace", 16), ("mixed", "naive", 8),
               ("07_sdfunction", "implicit", 4), ("06_gridsdf", "implicit", 4),
               ("sdf_small", "implicit", 4)]
@@ -194,12 +195,15 @@ def test_cameras_bit_exact(vpt, scenes, camera, shader):
 @pytest.mark.parametrize("scene,shader,res,bounces,spp,size", [
     ("03_volume", "volpathtrace", 1280, 64, 4, (1280, 533)),
     ("01_surface", "pathtrace", 720, 4, 2, (720, 300)),
+    ("02_rollingteapot", "pathtrace", 720, 4, 2, (720, 300)),
+    ("04_head1", "volpathtrace", 720, 4, 2, (720, 720)),
     ("05_head1ss", "volpathtrace", 1280, 64, 2, (1280, 1280)),
     ("06_gridsdf", "implicit", 1280, 4, 2, (1280, 533)),
     ("07_sdfunction", "implicit", 1920, 4, 2, (1920, 800))])
 def test_full_size_render_is_bit_exact(vpt, scenes, scene, shader, res, bounces, spp, size):
     """Every BASELINE.json configuration at the size bench.py runs it (03_volume is the headline:
-    volpathtrace, 1280x533, 64 bounces), for as many samples as the oracle renders in a few seconds:
+    volpathtrace, 1280x533, 64 bounces) plus the two remaining tests/ scenes at the size of
+    scripts/run.sh:2,4 (all seven scenes of north_star), for as many samples as the oracle renders in a few seconds:
     image sums and generator states equal the reference CPU path's bit for bit."""
     if util.scene_path(scene) is None:
         pytest.skip(f"{scene}.vptscene not built")

@@ -23,6 +23,22 @@
 // visited leaves are exactly the reference's. Root boxes (scene, instance) are
 // tested explicitly when they are entered, as the reference does.
 //
+// Wide nodes. A ray whose origin and 1/d are finite ("wide" below) walks the 4-slot collapse
+// of the same tree (dscene.cuh `wnodes`): one 128-byte record per visit, four slab tests, the
+// passing slots pushed in the reference's visit order for the ray's sign octant. It reaches
+// exactly the leaves the reference reaches, in the same order: for such a ray every slab term
+// (b - o) * (1/d) is a monotone function of the box coordinate b (float subtraction and
+// multiplication round monotonically, nothing is NaN), a descendant's box lies inside its
+// ancestors' boxes coordinate by coordinate (boxes are exact float min / max unions), hence
+// t0(child) >= t0(ancestor) and hi(child) <= hi(ancestor), and tmax only shrinks: a node that
+// passes its own test at its pop time implies that every ancestor passed at its (earlier) pop
+// time. So the intermediate boxes the collapse drops never decide anything, and the per-slot
+// test + pop-time re-check is the reference's test of that node. For the same reason
+// min(it_min, it_max) is the term of the box face on the near side of the sign of 1/d, so the
+// near / far faces are picked by ADDRESS (which f4 of the record) and the six selects go.
+// Rays with a zero direction component (1/d infinite -> NaN products, ternary min / max
+// semantics) keep the binary records and the code above.
+//
 // Instances. The reference has no per-instance box test: every instance of a
 // visited scene leaf gets its ray transformed (3 IEEE divisions for 1/d) and its
 // root box tested in object space. Here a scene leaf first tests the ray against
@@ -89,6 +105,29 @@ constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
 // component keep the ternaries, whose NaN behaviour the reference depends on.
 // `t0` (entry distance, independent of tmax) feeds the pop-time re-check.
 constexpr float box_slack = 1.00000024f;
+// max / min of two non-NaN floats (device: one FMNMX; equals the reference's ternaries up to
+// the sign of a zero, which no comparison below can see)
+VPT_FN float fmax2(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return fmaxf(a, b);
+#else
+  return a > b ? a : b;
+#endif
+}
+VPT_FN float fmin2(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return fminf(a, b);
+#else
+  return a < b ? a : b;
+#endif
+}
+VPT_FN int popc4(unsigned v) {
+#if defined(__CUDA_ARCH__)
+  return __popc(v);
+#else
+  return __builtin_popcount(v);
+#endif
+}
 VPT_FN bool intersect_box(f3 o, f3 dinv, float tmin, float tmax, f4 n0, f4 n1, bool plain,
     float& t0) {
   VPT_WORK(box_tests, 1);
@@ -173,7 +212,8 @@ inline bool vpt_cull_check_on = false;
 inline void vpt_cull_check(const DScene& sc, int instance, const ray3& ray, float tmax);
 #endif
 
-constexpr int ref_leaf = 0, ref_instance = 1, ref_sentinel = 2;
+constexpr int ref_leaf = 0, ref_instance = 1, ref_sentinel = 2, ref_empty = 3;
+constexpr int wide_none = (int)0x80000001;  // "this BVH has no wide nodes" (never a valid ref)
 VPT_FN constexpr int make_ref(int payload, int tag) { return ~((payload << 2) | tag); }
 constexpr int leaf_start_limit = 1 << 26;  // f4 index of a leaf's first primitive record
 #if !defined(VPT_TRAV_POPS)
@@ -188,6 +228,8 @@ struct trav_t {
   f3    wdinv;       // 1 / d of the world-space ray, kept so leaving an instance costs no divisions
   float tmin, tmax;
   bool  plain, wplain;  // all of dinv finite (see intersect_box), for the current / world ray
+  bool  wide, wwide;    // this space's walk uses the wide nodes (origin and dinv finite)
+  int   oct, woct;      // sign octant of dinv: bit k set if dinv[k] < 0
   bool  cull;           // world-space instance culling allowed for this ray
   float omax;           // largest |coordinate| of the world-space origin
   int   kind;        // -1: scene level, else the element kind of the entered shape
@@ -204,16 +246,56 @@ struct trav_t {
     wdinv = dinv, wplain = plain;
     omax  = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
     cull  = plain && vfinite(omax);
+    oct   = octant(dinv);
+    wide  = plain && all_finite(o) && sc.scene_wroot != wide_none;
+    wwide = wide, woct = oct;
     kind = -1, inst = -1, cur = 0;
     if (first >= 0) {
       st.push(cur++, make_ref(first, ref_instance), 0);
     } else if (sc.num_instances > 0) {
       float t0;
       if (intersect_box(o, dinv, tmin, tmax, sc.scene_box0, sc.scene_box1, plain, t0))
-        st.push(cur++, sc.scene_root, t0);
+        st.push(cur++, wide ? sc.scene_wroot : sc.scene_root, t0);
     }
   }
   VPT_FN bool done() const { return cur == 0; }
+  static VPT_FN int octant(f3 di) {
+    return (di.x < 0 ? 1 : 0) | (di.y < 0 ? 2 : 0) | (di.z < 0 ? 4 : 0);
+  }
+
+  // One visit of a wide node (see the header): four slab tests, pushes in visit order.
+  VPT_FN void visit_wide(const DScene& sc, int e, stack_t st) {
+    VPT_WORK(wide_visits, 1);
+    auto p  = sc.wnodes + 8 * (size_t)e;
+    int  sx = oct & 1, sy = (oct >> 1) & 1, sz = oct >> 2;
+    auto nx = ld4(p + 3 * sx), fx = ld4(p + 3 - 3 * sx);
+    auto ny = ld4(p + 1 + 3 * sy), fy = ld4(p + 4 - 3 * sy);
+    auto nz = ld4(p + 2 + 3 * sz), fz = ld4(p + 5 - 3 * sz);
+    auto rf = ld4(p + 6);
+    auto ow = (unsigned)ld1(reinterpret_cast<const int*>(p + 7) + (oct >> 1)) >> ((oct & 1) * 16);
+    unsigned m = 0;
+#define VPT_WIDE_SLOT(k, c)                                                                     \
+  float lo##k = fmax2(fmax2(fmax2((nx.c - o.x) * dinv.x, (ny.c - o.y) * dinv.y),               \
+                          (nz.c - o.z) * dinv.z), tmin);                                      \
+  float hi##k = fmin2(fmin2(fmin2((fx.c - o.x) * dinv.x, (fy.c - o.y) * dinv.y),               \
+                          (fz.c - o.z) * dinv.z), tmax) * box_slack;                          \
+  int      r##k = f2i(rf.c);                                                                    \
+  unsigned h##k = (ow >> (4 * k)) & 15u;                                                        \
+  bool     p##k = lo##k <= hi##k && r##k != make_ref(0, ref_empty);                             \
+  m |= p##k ? h##k : 0u;
+    VPT_WIDE_SLOT(0, x)
+    VPT_WIDE_SLOT(1, y)
+    VPT_WIDE_SLOT(2, z)
+    VPT_WIDE_SLOT(3, w)
+#undef VPT_WIDE_SLOT
+    VPT_WORK(wide_slot_tests, 4);
+    // the first-visited slot (rank 0) goes on top: position = passing slots of higher rank
+    if (p0) st.push(cur + popc4(m & (0u - (h0 << 1))), r0, lo0);
+    if (p1) st.push(cur + popc4(m & (0u - (h1 << 1))), r1, lo1);
+    if (p2) st.push(cur + popc4(m & (0u - (h2 << 1))), r2, lo2);
+    if (p3) st.push(cur + popc4(m & (0u - (h3 << 1))), r3, lo3);
+    cur += popc4(m);
+  }
 
   // One round: pop until this lane holds a leaf or an instance to enter, its stack is empty
   // or it has popped `trav_pops` entries; then enter the instance / process the leaf. The
@@ -243,7 +325,11 @@ struct trav_t {
       int   e  = en.ref;
       float te = en.t0;
       if (e >= 0) {
-        if (te <= tmax * box_slack) {
+        if (!(te <= tmax * box_slack)) {
+          VPT_WORK(stale_node_pops, 1);
+        } else if (wide) {
+          visit_wide(sc, e, st);
+        } else {
           VPT_WORK(node_visits, 1);
           auto p  = sc.nodes + 4 * (size_t)e;
           auto a0 = ld4(p), a1 = ld4(p + 1), b0 = ld4(p + 2), b1 = ld4(p + 3);
@@ -277,6 +363,7 @@ struct trav_t {
     if (enter == -2) {  // back to the world-space ray
       o = ray.o, d = ray.d;
       dinv = wdinv, plain = wplain;
+      wide = wwide, oct = woct;
       kind = -1;
       enter = -1;
       again = cur != 0 && pops != 0;
@@ -297,10 +384,12 @@ struct trav_t {
         float t0;
         if (intersect_box(lo, li, tmin, tmax, r0, r1, lp, t0)) {
           o = lo, d = ld, dinv = li, plain = lp;
+          wide = lp && all_finite(lo) && f2i(r1.w) != wide_none;
+          oct  = octant(li);
           inst = enter;
           kind = f2i(c1.w);
           st.push(cur++, make_ref(0, ref_sentinel), 0);
-          st.push(cur++, f2i(r1.z), t0);
+          st.push(cur++, wide ? f2i(r1.w) : f2i(r1.z), t0);
         }
       }
     }

@@ -10,6 +10,15 @@
 //              (scene BVH: first slot of scene_leaves). `axis` is the split axis
 //              of the node the record belongs to. All shape BVHs and the scene
 //              BVH are concatenated. One 64-byte fetch per visited node.
+//   wnodes     8 x f4 (128 bytes) per WIDE node: up to four descendants of one binary
+//              node (its two children, the widest of them expanded again while slots
+//              are free), as SoA so that one 16-byte load holds one box coordinate of
+//              all four slots: {min.x[4]} {min.y[4]} {min.z[4]} {max.x[4]} {max.y[4]}
+//              {max.z[4]} {ref[4]} {order[8 x 16 bit]}. Slot refs are wide-node indices
+//              or the same leaf refs as above (unused slot: ref_empty). `order` holds,
+//              for each of the 8 sign octants of 1/d, the one-hot rank (4 bits per
+//              slot) in which the reference's depth-first walk reaches the slots
+//              (bvh.cuh). Rays whose 1/d is not finite walk `nodes` instead.
 //   prims      primitives gathered in BVH leaf order, vertex positions inline:
 //              quad = 4 x f4 {p_k.xyz, payload}, triangle = 3 x f4;
 //              payload of the first f4 = element index.
@@ -18,8 +27,8 @@
 //              largest |ray origin| culling is valid for (-1: never cull)}
 //   inst_trav  4 x f4 per instance: columns of inverse(frame, non_rigid) in xyz;
 //              w = {0 or -1 (no geometry), shape kind, shape id, material id}
-//   inst_root  2 x f4 per instance: the shape BVH's root box and ref
-//              {min.xyz, max.x} {max.yz, ref, 0}
+//   inst_root  2 x f4 per instance: the shape BVH's root box and refs
+//              {min.xyz, max.x} {max.yz, ref in nodes, ref in wnodes}
 //   inst_frame 4 x f4 per instance: forward frame columns.
 // The reference layout this replaces: bvh_data / shape_data / instance_data
 // (yocto_bvh.h:73-92, yocto_shape.h:74, yocto_scene.h:142-148).
@@ -34,6 +43,7 @@ enum shape_kind : int { kind_empty = 0, kind_triangles = 1, kind_quads = 2 };
 struct DScene {
   // acceleration
   const f4*  nodes;
+  const f4*  wnodes;
   const f4*  prims;
   const f4*  scene_leaves;
   const f4*  inst_trav;
@@ -41,6 +51,7 @@ struct DScene {
   const f4*  inst_frame;
   f4         scene_box0, scene_box1;  // root box of the scene BVH {min.xyz, max.x} {max.yz, 0, 0}
   int        scene_root;              // ref of the scene BVH root (valid if num_instances > 0)
+  int        scene_wroot;             // the same root in `wnodes` (wide_none: walk `nodes`)
   int        num_instances;
   // shapes for shading: 2 x i4 per shape {kind, pos, nrm, tex} {col, elem, 0, 0}
   const i4*    shapes;

@@ -40,6 +40,10 @@ VPT_FN int sample_uniform(int size, float r) { return vclamp((int)(r * size), 0,
 
 // sample_lights (yocto_pathtrace.cpp:312-350)
 VPT_CALL f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2 ruv) {
+  // no emitters: the reference indexes an empty vector here (UB on the host); on the device an
+  // out-of-range read can poison the context, so the direction is zero, which ends the path
+  // exactly as `incoming == 0` does (yocto_pathtrace.cpp:736)
+  if (sc.num_lights <= 0) return {0, 0, 0};
   auto light_id = sample_uniform(sc.num_lights, rl);
   auto l0 = ld4(sc.lights + 2 * light_id), l1 = ld4(sc.lights + 2 * light_id + 1);
   if (l0.x != invalidid) {
@@ -80,6 +84,7 @@ VPT_FN float sample_lights_pdf(const DScene& sc, f3 position, f3 direction,
     int spheretrace_maxiter, stack_t st, unsigned long long* ray_counter = nullptr) {
   auto pdf = 0.0f;
   VPT_WORK(lightpdf_calls, 1);
+  if (sc.num_lights <= 0) return 0;  // see sample_lights
   for (auto li = 0; li < sc.num_lights; li++) {
     auto l0 = ld4(sc.lights + 2 * li), l1 = ld4(sc.lights + 2 * li + 1);
     if (l0.x != invalidid) {

@@ -13,6 +13,7 @@ inline const char* cudaGetErrorString(cudaError_t) { return "host pool error"; }
 #include <cuda_runtime.h>
 #endif
 
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -109,7 +110,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   if (in.num_shapes > 0 && !in.shape_bvhs)
     return fail(VPT_ERR_INVALID, "shape_bvhs is null");
 
-  std::vector<f4>  nodes, prims, inst_trav, inst_frame, vcol, materials, cameras, environments;
+  std::vector<f4>  nodes, wnodes, prims, inst_trav, inst_frame, vcol, materials, cameras, environments;
   std::vector<f4>  vol_instances, volumes, sdfs, texf;
   std::vector<f4>  scene_leaves, inst_root;
   std::vector<i4>  shapes, elems, textures, lights;
@@ -119,8 +120,11 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   // Appends one BVH in the child-pair layout of dscene.cuh. `leaf_base` / `leaf_stride`
   // rebase a leaf's `start` (f4 index of its first primitive record, or its first
   // scene_leaves slot). Returns the root's {box, ref} through root0 / root1.
+  // VPT_NO_WIDE=1: upload without the wide nodes, every ray walks the binary records (A/B runs)
+  const char* no_wide_env = getenv("VPT_NO_WIDE");
+  const bool  wide_on     = !(no_wide_env && atoi(no_wide_env) != 0);
   auto push_bvh = [&](const vpt_bvh_desc& bvh, int leaf_base, int leaf_stride, f4& root0,
-                      f4& root1, std::string& why) -> bool {
+                      f4& root1, int& wocc, std::string& why) -> bool {
     int              pair_base = (int)(nodes.size() / 4);
     std::vector<int> pair_of(bvh.num_nodes, -1);
     int              npairs = 0;
@@ -162,14 +166,128 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     int rr = 0;
     if (!ref_of(0, rr)) return false;
     root0 = box0(bvh.nodes[0]);
-    root1 = {bvh.nodes[0].bbox_max[1], bvh.nodes[0].bbox_max[2], i2f(rr), i2f(0)};
+    root1 = {bvh.nodes[0].bbox_max[1], bvh.nodes[0].bbox_max[2], i2f(rr), i2f(wide_none)};
+    // ---- the same tree collapsed into 4-slot wide nodes (dscene.cuh, bvh.cuh) ----
+    // A wide node starts from a binary node's two children and, while a slot is free,
+    // replaces the internal slot with the largest box by that node's two children, in place,
+    // so slots stay in the tree's left-to-right order. The order table records, for every
+    // sign octant of 1/d, where the reference's walk (near child first by the sign on each
+    // node's split axis, yocto_bvh.cpp:743-749) reaches each slot.
+    wocc = 0;
+    if (!wide_on) return true;
+    for (int n = 0; n < bvh.num_nodes; n++)
+      for (int k = 0; k < 3; k++)
+        if (!(bvh.nodes[n].bbox_min[k] == bvh.nodes[n].bbox_min[k]) ||
+            !(bvh.nodes[n].bbox_max[k] == bvh.nodes[n].bbox_max[k]))
+          return true;  // a NaN box: the ternary min / max of the binary walk decide
+    if (!bvh.nodes[0].internal) {
+      root1.w = i2f(rr);  // a single leaf is its own wide root
+      return true;
+    }
+    int              wide_base = (int)(wnodes.size() / 8);
+    std::vector<int> wide_of(bvh.num_nodes, -1), queue, nslots_of;
+    auto wide_ref = [&](int n) {
+      if (wide_of[n] < 0) {
+        wide_of[n] = wide_base + (int)queue.size();
+        queue.push_back(n);
+      }
+      return wide_of[n];
+    };
+    struct lnode {
+      int node, l, r;  // l < 0: a slot
+    };
+    root1.w = i2f(wide_ref(0));
+    for (size_t qi = 0; qi < queue.size(); qi++) {
+      int  n    = queue[qi];
+      auto tree = std::vector<lnode>{{n, 1, 2}, {bvh.nodes[n].start, -1, -1},
+          {bvh.nodes[n].start + 1, -1, -1}};
+      int nslots = 2;
+      while (nslots < 4) {
+        int    best = -1;
+        double best_area = -1;
+        for (int i = 0; i < (int)tree.size(); i++) {
+          auto& b = bvh.nodes[tree[i].node];
+          if (tree[i].l >= 0 || !b.internal) continue;
+          double dx = (double)b.bbox_max[0] - b.bbox_min[0], dy = (double)b.bbox_max[1] - b.bbox_min[1],
+                 dz = (double)b.bbox_max[2] - b.bbox_min[2];
+          double area = dx * dy + dy * dz + dz * dx;
+          if (!(area >= 0)) area = 0;
+          if (area > best_area) best = i, best_area = area;
+        }
+        if (best < 0) break;
+        int start    = bvh.nodes[tree[best].node].start;
+        tree[best].l = (int)tree.size(), tree[best].r = (int)tree.size() + 1;
+        tree.push_back({start, -1, -1});
+        tree.push_back({start + 1, -1, -1});
+        nslots++;
+      }
+      // slots in left-to-right order; visit sequence per octant
+      std::vector<int> slot_of(tree.size(), -1), slots;
+      struct walker {
+        const std::vector<lnode>& tree;
+        const vpt_bvh_desc&       bvh;
+        void run(int i, int oct, std::vector<int>& seq) const {
+          if (tree[i].l < 0) {
+            seq.push_back(i);
+            return;
+          }
+          bool flip = oct >= 0 && ((oct >> ((int)bvh.nodes[tree[i].node].axis & 3)) & 1);
+          run(flip ? tree[i].r : tree[i].l, oct, seq);
+          run(flip ? tree[i].l : tree[i].r, oct, seq);
+        }
+      } walk{tree, bvh};
+      walk.run(0, -1, slots);
+      for (int k = 0; k < (int)slots.size(); k++) slot_of[slots[k]] = k;
+      f4  rec[8];
+      int refs[4] = {make_ref(0, ref_empty), make_ref(0, ref_empty), make_ref(0, ref_empty),
+          make_ref(0, ref_empty)};
+      float box[6][4] = {};
+      for (int k = 0; k < (int)slots.size(); k++) {
+        int   node = tree[slots[k]].node;
+        auto& b    = bvh.nodes[node];
+        for (int c = 0; c < 3; c++) box[c][k] = b.bbox_min[c], box[3 + c][k] = b.bbox_max[c];
+        if (b.internal) {
+          if (b.start < 1 || b.start + 1 >= bvh.num_nodes) {
+            why = "bvh child link out of range";
+            return false;
+          }
+          refs[k] = wide_ref(node);
+        } else if (!ref_of(node, refs[k])) {
+          return false;
+        }
+      }
+      for (int c = 0; c < 6; c++) rec[c] = {box[c][0], box[c][1], box[c][2], box[c][3]};
+      rec[6] = {i2f(refs[0]), i2f(refs[1]), i2f(refs[2]), i2f(refs[3])};
+      unsigned order[4] = {0, 0, 0, 0};
+      for (int oct = 0; oct < 8; oct++) {
+        std::vector<int> seq;
+        walk.run(0, oct, seq);
+        unsigned bits = 0;
+        for (int rank = 0; rank < (int)seq.size(); rank++) bits |= (1u << rank) << (4 * slot_of[seq[rank]]);
+        order[oct >> 1] |= bits << ((oct & 1) * 16);
+      }
+      rec[7] = {i2f((int)order[0]), i2f((int)order[1]), i2f((int)order[2]), i2f((int)order[3])};
+      for (auto& r : rec) wnodes.push_back(r);
+      nslots_of.push_back(nslots);
+    }
+    // stack entries a walk of this wide tree can hold (children are queued after parents)
+    std::vector<int> occ(queue.size(), 0);
+    for (int qi = (int)queue.size() - 1; qi >= 0; qi--) {
+      int deepest = 0;
+      auto rf = wnodes[8 * (size_t)(wide_base + qi) + 6];
+      int  r4[4] = {f2i(rf.x), f2i(rf.y), f2i(rf.z), f2i(rf.w)};
+      for (int k = 0; k < 4; k++)
+        if (r4[k] >= 0) deepest = occ[r4[k] - wide_base] > deepest ? occ[r4[k] - wide_base] : deepest;
+      occ[qi] = nslots_of[qi] - 1 + deepest > nslots_of[qi] ? nslots_of[qi] - 1 + deepest : nslots_of[qi];
+    }
+    wocc = occ[0];
     return true;
   };
 
   // ---- shapes: vertex pools, element indices, leaf-ordered primitive records ----
   std::vector<int> shape_kind(in.num_shapes, kind_empty);
   std::vector<f4>  shape_root0(in.num_shapes, f4{0, 0, 0, 0}), shape_root1(in.num_shapes, f4{0, 0, 0, 0});
-  int              max_shape_depth = 0;
+  int              max_shape_depth = 0, max_shape_wocc = 0;
   for (int s = 0; s < in.num_shapes; s++) {
     auto& sh = in.shapes[s];
     if (sh.num_points > 0 || sh.num_lines > 0)
@@ -236,9 +354,11 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
       if (!node.internal && (node.start < 0 || node.start + node.num > bvh.num_primitives))
         return fail(VPT_ERR_INVALID, "bvh leaf out of range in shape " + std::to_string(s));
     }
-    auto why = std::string{};
-    if (!push_bvh(bvh, prim_base, stride, shape_root0[s], shape_root1[s], why))
+    auto why  = std::string{};
+    int  wocc = 0;
+    if (!push_bvh(bvh, prim_base, stride, shape_root0[s], shape_root1[s], wocc, why))
       return fail(VPT_ERR_UNSUPPORTED, why + " (shape " + std::to_string(s) + ")");
+    max_shape_wocc = wocc > max_shape_wocc ? wocc : max_shape_wocc;
   }
 
   // ---- instances + scene bvh ----------------------------------------------------
@@ -292,7 +412,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
         (float)(wmax[0] + margin)};
     b1 = {(float)(wmax[1] + margin), (float)(wmax[2] + margin), i2f(i), (float)(100 * scale)};
   };
-  int scene_root = 0, scene_depth = 0, scene_leaf = 0;
+  int scene_root = 0, scene_wroot = wide_none, scene_depth = 0, scene_leaf = 0, scene_wocc = 0;
   f4  scene_box0{0, 0, 0, 0}, scene_box1{0, 0, 0, 0};
   if (in.num_instances > 0) {
     auto& bvh = in.scene_bvh;
@@ -317,22 +437,31 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     }
     auto why = std::string{};
     f4   root1;
-    if (!push_bvh(bvh, 0, 1, scene_box0, root1, why))
+    if (!push_bvh(bvh, 0, 1, scene_box0, root1, scene_wocc, why))
       return fail(VPT_ERR_UNSUPPORTED, why + " (scene bvh)");
-    scene_box1 = {root1.x, root1.y, 0, 0};
-    scene_root = f2i(root1.z);
+    scene_box1  = {root1.x, root1.y, 0, 0};
+    scene_root  = f2i(root1.z);
+    scene_wroot = f2i(root1.w);
   }
   // one stack for both levels (bvh.cuh): a sibling per scene level, the queued
   // instances of one scene leaf, the sentinel, then a sibling per shape level
   out.stack_depth = scene_depth + 1 + scene_leaf + 1 + max_shape_depth + 1;
+  // the wide walk pushes up to four slots per visit
+  int wide_depth = (scene_wocc > 1 ? scene_wocc : 1) + scene_leaf + 1 +
+                   (max_shape_wocc > 1 ? max_shape_wocc : 1) + 1;
+  out.stack_depth = wide_depth > out.stack_depth ? wide_depth : out.stack_depth;
   if (out.stack_depth > vpt_stack_depth)
     return fail(VPT_ERR_UNSUPPORTED, "bvh deeper than the device traversal stack (" +
                                          std::to_string(out.stack_depth) + " > " +
                                          std::to_string(vpt_stack_depth) + ")");
 
   // ---- materials, textures ---------------------------------------------------------
+  auto tex_ok = [&](int handle) { return handle >= -1 && handle < in.num_textures; };
   for (int m = 0; m < in.num_materials; m++) {
     auto& mt = in.materials[m];
+    // SDF scenes of the reference carry texture handles past the texture list
+    // (tests/06_gridsdf: color_tex 1, 2 with one texture); eval_material(scene, int) ignores
+    // textures, so those are legal there and only instanced (mesh) materials are checked below
     materials.push_back({i2f(mt.type), mt.emission[0], mt.emission[1], mt.emission[2]});
     materials.push_back({mt.color[0], mt.color[1], mt.color[2], mt.roughness});
     materials.push_back({mt.metallic, mt.ior, mt.scattering[0], mt.scattering[1]});
@@ -341,8 +470,17 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
         i2f(mt.scattering_tex)});
     materials.push_back({i2f(mt.normal_tex), 0, 0, 0});
   }
+  for (int i = 0; i < in.num_instances; i++) {
+    auto& mt = in.materials[in.instances[i].material];
+    if (!tex_ok(mt.emission_tex) || !tex_ok(mt.color_tex) || !tex_ok(mt.roughness_tex) ||
+        !tex_ok(mt.scattering_tex) || !tex_ok(mt.normal_tex))
+      return fail(VPT_ERR_INVALID, "material " + std::to_string(in.instances[i].material) +
+                                       " references a missing texture");
+  }
   for (int t = 0; t < in.num_textures; t++) {
     auto&  tx = in.textures[t];
+    if (tx.width < 0 || tx.height < 0 || ((tx.pixelsf || tx.pixelsb) && (tx.width == 0 || tx.height == 0)))
+      return fail(VPT_ERR_INVALID, "texture " + std::to_string(t) + " has a bad size");
     size_t n  = (size_t)tx.width * tx.height;
     if (tx.pixelsf) {
       textures.push_back({tx.width, tx.height, (tx.linear ? 1 : 0) | 2, (int)texf.size()});
@@ -379,7 +517,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     auto& ev    = in.environments[e];
     auto  frame = to_frame(ev.frame);
     auto  inv   = inverse_frame(frame, false);  // inverse(environment.frame): rigid
-    if (ev.emission_tex >= in.num_textures)
+    if (!tex_ok(ev.emission_tex))
       return fail(VPT_ERR_INVALID, "environment texture out of range");
     environments.push_back(pack(frame.x, 0)), environments.push_back(pack(frame.y, 0));
     environments.push_back(pack(frame.z, 0)), environments.push_back(pack(frame.o, 0));
@@ -404,6 +542,8 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   // ---- sdf grids and functions -------------------------------------------------------
   for (int v = 0; v < in.num_volumes; v++) {
     auto&  vol = in.volumes[v];
+    if (vol.whd[0] <= 0 || vol.whd[1] <= 0 || vol.whd[2] <= 0 || !vol.voxels)
+      return fail(VPT_ERR_INVALID, "sdf grid " + std::to_string(v) + " is empty");
     size_t n   = (size_t)vol.whd[0] * vol.whd[1] * vol.whd[2];
     volumes.push_back({i2f(vol.whd[0]), i2f(vol.whd[1]), i2f(vol.whd[2]), vol.res});
     volumes.push_back({i2f((int)voxels.size()), 0, 0, 0});
@@ -434,6 +574,13 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     sdfs.push_back({sd.whd[0], sd.whd[1], sd.whd[2], 0});
   }
 
+  // offsets into the pools are stored as int
+  const size_t int_max = 0x7fffffff;
+  if (texf.size() > int_max || texb.size() / 4 > int_max || voxels.size() > int_max ||
+      cdf.size() > int_max || vpos.size() / 3 > int_max || elems.size() > int_max ||
+      nodes.size() > int_max)
+    return fail(VPT_ERR_UNSUPPORTED, "scene pools exceed 2^31 elements");
+
   // ---- to the device -----------------------------------------------------------------
   auto& d = out.d;
   auto& p = out.pool;
@@ -441,6 +588,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
 #define VPT_UP(vec, field) \
   if (e == cudaSuccess) e = p.upload(vec, &d.field)
   VPT_UP(nodes, nodes);
+  VPT_UP(wnodes, wnodes);
   VPT_UP(prims, prims);
   VPT_UP(scene_leaves, scene_leaves);
   VPT_UP(inst_trav, inst_trav);
@@ -472,6 +620,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
         std::string("scene upload failed: ") + cudaGetErrorString(e));
   }
   d.scene_root        = scene_root;
+  d.scene_wroot       = scene_wroot;
   d.scene_box0 = scene_box0, d.scene_box1 = scene_box1;
   d.num_instances     = in.num_instances;
   d.num_environments  = in.num_environments;

@@ -519,6 +519,9 @@ int vpt_cuda_trace_samples(vpt_scene* scene, vpt_state* state, const vpt_params*
     return set_error(VPT_ERR_INVALID, "sampler unknown");  // get_shader, yocto_pathtrace.cpp:948
   if (params->camera < 0 || params->camera >= scene->flat.num_cameras)
     return set_error(VPT_ERR_INVALID, "camera index out of range");
+  // the wavefront packs the bounce counter in 16 bits (the CLI's range is [1, 128])
+  if (params->bounces < 1 || params->bounces > 65535)
+    return set_error(VPT_ERR_INVALID, "bounces out of range [1, 65535]");
   state->stats = vpt_trace_stats{};
   int todo = std::min(nsamples, params->samples - state->samples);
   if (todo <= 0) return VPT_OK;  // yocto_pathtrace.cpp:1055

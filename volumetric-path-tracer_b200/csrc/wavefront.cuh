@@ -172,6 +172,12 @@ struct wavefront_buffers {
   cudaError_t reserve(int slots, int npipes) {
     if (capacity >= slots && pipes == npipes) return cudaSuccess;
     release();
+    auto e = reserve_all(slots, npipes);
+    // a half-built set of buffers must never satisfy the early-out above
+    if (e != cudaSuccess) release();
+    return e;
+  }
+  cudaError_t reserve_all(int slots, int npipes) {
     auto e = cudaMalloc(&rec, sizeof(f4) * wf_rec * (size_t)slots);
     if (e != cudaSuccess) return e;
     capacity = slots, pipes = npipes;  // from here on release() frees what exists
@@ -290,7 +296,8 @@ constexpr int wf_susp_head = 7;
 inline int wf_susp_record_f4(int stack_depth) { return wf_susp_head + (stack_depth + 1) / 2; }
 
 __device__ __forceinline__ void wf_suspend_ray(f4* rec, const trav_t& t, stack_t st) {
-  int bits = (t.plain ? 1 : 0) | (t.wplain ? 2 : 0) | (t.cull ? 4 : 0) | (t.h.hit ? 8 : 0);
+  int bits = (t.plain ? 1 : 0) | (t.wplain ? 2 : 0) | (t.cull ? 4 : 0) | (t.h.hit ? 8 : 0) |
+             (t.wide ? 16 : 0) | (t.wwide ? 32 : 0) | (t.oct << 8) | (t.woct << 12);
   rec[0] = {t.o.x, t.o.y, t.o.z, t.d.x};
   rec[1] = {t.d.y, t.d.z, t.dinv.x, t.dinv.y};
   rec[2] = {t.dinv.z, t.wdinv.x, t.wdinv.y, t.wdinv.z};
@@ -308,6 +315,7 @@ __device__ __forceinline__ void wf_resume_ray(const f4* rec, trav_t& t, stack_t 
   t.tmin = d.x, t.tmax = d.y, t.omax = d.z;
   int bits = f2i(d.w);
   t.plain = bits & 1, t.wplain = bits & 2, t.cull = bits & 4;
+  t.wide = bits & 16, t.wwide = bits & 32, t.oct = (bits >> 8) & 7, t.woct = (bits >> 12) & 7;
   t.kind = f2i(e.x), t.inst = f2i(e.y), t.cur = f2i(e.z);
   t.h = hit_t{f2i(e.w), f2i(f.x), {f.y, f.z}, f.w, (bits & 8) != 0};
   for (int i = 0; i < t.cur; i += 2) {
@@ -478,6 +486,10 @@ constexpr int wf_refill_sdf = 4;             // sphere tracing (B200: 07_sdfunct
 #define VPT_WF_SUSPEND_AT 20
 #endif
 constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in place)
+#if !defined(VPT_WF_LEAF_HOLD)
+#define VPT_WF_LEAF_HOLD 0
+#endif
+constexpr int wf_leaf_hold = VPT_WF_LEAF_HOLD;  // 0: test a leaf in the round that reaches it
 #if !defined(VPT_WF_SDF_STEPS)
 #define VPT_WF_SDF_STEPS 4
 #endif
@@ -485,7 +497,8 @@ constexpr int wf_sdf_steps = VPT_WF_SDF_STEPS;
 
 template <int S>
 __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
-    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
+    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at,
+        int leaf_hold) {
   extern __shared__ int stack_mem[];
 #if defined(VPT_WF_COOP_LEAVES)
   __shared__ unsigned char leaf_tab[wf_block / 32][32 * 8];
@@ -519,6 +532,12 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
 #endif
   t.cur       = 0;
   sp.finished = true;
+  // Leaf postponement: a lane that reaches a mesh leaf HOLDS it (pops nothing more) until at
+  // least `leaf_hold` lanes of the warp hold one or no lane can descend any further; then all
+  // of them run the primitive tests together. ncu r01c: the (long) leaf code ran at ~5 of 32
+  // lanes when every round ended with the tests of whoever had found a leaf. A ray's own
+  // sequence of operations is unchanged (it does nothing between finding and testing a leaf).
+  int held = 0;
   while (running) {
     unsigned idle = __ballot_sync(full, !has_ray);
     if (more && (__popc(idle) >= (sdf ? wf_refill_sdf : wf_refill))) {
@@ -555,14 +574,23 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
         if (has_ray && !sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
     } else {
 #if !defined(VPT_WF_COOP_LEAVES)
-      if (has_ray && !t.done()) t.round(sc, ray, st);
+      bool moving = has_ray && held == 0 && !t.done();
+      if (moving) held = t.descend(sc, ray, st);
+      unsigned holders = __ballot_sync(full, held != 0);
+      if (holders) {
+        unsigned movers = __ballot_sync(full, has_ray && held == 0 && !t.done());
+        if (__popc(holders) >= leaf_hold || movers == 0) {
+          if (held != 0) t.test_leaf(sc, held);
+          held = 0;
+        }
+      }
 #else
       int leaf = 0;
       if (has_ray && !t.done()) leaf = t.descend(sc, ray, st);
       wf_test_leaves_warp(sc, t, leaf, leaf_tab[threadIdx.x >> 5]);
 #endif
     }
-    bool     retire   = has_ray && (sdf ? sp.done() : t.done());
+    bool     retire   = has_ray && (sdf ? sp.done() : (held == 0 && t.done()));
     unsigned retiring = __ballot_sync(full, retire);
     if (retire) {
       isect_t isec;
@@ -595,6 +623,10 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
     }
     unsigned walking = __ballot_sync(full, has_ray);
     if (!more && walking && __popc(walking) <= (sdf ? suspend_at : suspend_mesh)) {
+      if constexpr (!sdf) {
+        if (held != 0) t.test_leaf(sc, held);  // a parked walk carries no held leaf
+        held = 0;
+      }
       // park what is left of this warp for the next iteration's launch
       int n = __popc(walking), leader = __ffs(walking) - 1;
       int rank = __popc(walking & ((1u << lane) - 1));
@@ -897,6 +929,9 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   // lanes still walking at or below which a warp parks its rays once the queue is empty
   const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
+  // lanes that must hold a leaf before the warp runs the primitive tests (see the kernel)
+  const char* hold_env = getenv("VPT_WF_LEAF_HOLD");
+  int leaf_hold = hold_env ? atoi(hold_env) : wf_leaf_hold;
   // parked BVH walks need record pools (sphere tracing parks into the slot record itself)
 #if defined(VPT_WF_SUSPEND_MESH)
   if (persistent && !is_sdf_shader<S>()) {
@@ -938,7 +973,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (trace) trace->mark(grid);
       if (persistent)
         k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
-            scene.d, prm, w, p.cur, suspend_at);
+            scene.d, prm, w, p.cur, suspend_at, leaf_hold);
       else
         k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
       if (it == 0 && timed) cudaEventRecord(wf.k1, p.stream);
@@ -1017,6 +1052,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   stats->top_kernel_units    = top_rays;
   stats->rays_extend = stats->rays_lightpdf = 0;
   for (int i = 0; i < npipes; i++) {
+    if (wf.pipe[i].batches == 0) continue;  // a pipe without slots never wrote its counters
     auto c = wf.pipe[i].host_counters[(wf.pipe[i].batches - 1) & 1];
     stats->rays_extend += c->rays_extend - c->rays_resumed;
     stats->rays_lightpdf += c->rays_lightpdf;
