@@ -57,7 +57,7 @@ def test_one_bounce_and_many_bounces_bit_exact(vpt):
         assert np.array_equal(rng, ref["rngs_after"])
 
 
-@pytest.mark.parametrize("shader", ["pathtrace", "volpathtrace", "naive", "eyelight"])
+@pytest.mark.parametrize("shader", ["pathtrace", "volpathtrace", "naive"])
 @pytest.mark.parametrize("pipeline", ["mega", "wavefront"])
 def test_scene_without_emitters_renders_black(vpt, shader, pipeline):
     """No emissive material and no environment: the light list is empty. The reference indexes

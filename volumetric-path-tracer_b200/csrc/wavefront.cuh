@@ -73,29 +73,41 @@ struct wf_counters {
   unsigned long long rays_resumed;   // queue entries that were continuations, not new rays
 };
 
-// One 160-byte record per slot (5 aligned 32-byte sectors), fields in the order the
-// kernels touch them: extend reads the ray (sector 0) and writes the hit (sector 1);
-// shade / light-pdf read and write the rest. Keeping a slot's state contiguous matters
-// because the shade queue is class-sorted, i.e. slots are visited in scattered order:
-// nine separate SoA arrays cost nine half-used sectors per path (ncu r01: 1.0 GB of
-// DRAM traffic per k_wf_shade launch against 0.2 GB of state).
+// One 128-byte record per slot, 128-byte aligned = two 64-byte DRAM bursts, four 32-byte
+// sectors laid out by who writes them (ncu r01f / r02a: the former 160-byte record straddled
+// 3-4 bursts, k_wf_shade moved 586 B per slot for 320 B of state and k_wf_extend 157 B for 56):
+//   sector 0  the next ray + flags + remaining samples: written by shade / tail, READ by extend
+//   sector 1  the hit: written whole by extend (no partial-sector fill), read by shade
+//   sector 2  radiance and weight: shade / tail
+//   sector 3  pending MIS terms and the pixel's generator: shade / tail
+// The medium of a path inside a volume (volpathtrace) lives in a separate 64-byte record per
+// slot (`vol`), touched only when a path enters a volume or scatters inside one.
+// Keeping a slot's state contiguous matters because the shade queue is class-sorted, i.e.
+// slots are visited in scattered order: nine separate SoA arrays cost nine half-used sectors
+// per path (ncu r01: 1.0 GB of DRAM traffic per k_wf_shade launch against 0.2 GB of state).
 enum : int {
   wf_ray0 = 0,   // o.xyz, d.x
   wf_ray1 = 1,   // d.yz, flags, remaining samples
   wf_hit  = 2,   // instance, element, uv
-  wf_w1   = 3,   // weight.yz, vol_anisotropy, hit distance
+  wf_hit1 = 3,   // hit distance, hit flag, light pdf (k_wf_lightpdf), 0
   wf_rad  = 4,   // radiance.xyz, weight.x
-  wf_mis  = 5,   // pending f.xyz, bsdf pdf
-  wf_vol0 = 6, wf_vol1 = 7, wf_vol2 = 8,  // density, scattering, emission of the current volume
-  wf_rng  = 9,   // the pixel's PCG32 state while the slot is live
-  wf_rec  = 10
+  wf_w1   = 5,   // weight.yz, vol_anisotropy, 0
+  wf_mis  = 6,   // pending f.xyz, bsdf pdf
+  wf_rng  = 7,   // the pixel's PCG32 state while the slot is live
+  wf_rec  = 8,
+  wf_vol0 = 0, wf_vol1 = 1, wf_vol2 = 2,  // `vol` record: density, scattering, emission
+  wf_vol_rec = 4
 };
 
 // device pointers of one state's wavefront buffers
 struct wf_view {
   f4* rec;
+  f4* vol;
   __device__ __forceinline__ f4& at(int field, int slot) const {
     return rec[(size_t)slot * wf_rec + field];
+  }
+  __device__ __forceinline__ f4& vol_at(int field, int slot) const {
+    return vol[(size_t)slot * wf_vol_rec + field];
   }
   int *       queue_ext[2], *queue_pdf;
   int *       queue_shade, *sort_key;  // class-sorted slots; (class << 24 | rank) per entry
@@ -128,11 +140,13 @@ struct wavefront_buffers {
   bool        live     = false;
   int         capacity = 0, pipes = 0;
   f4*         rec = nullptr;
+  f4*         vol = nullptr;
   wf_pipe     pipe[wf_max_pipes];
   cudaEvent_t k0 = nullptr, k1 = nullptr;
   void release() {
     if (!capacity) return;
     cudaFree(rec);
+    if (vol) cudaFree(vol);
     for (auto& p : pipe) {
       if (p.queues) cudaFree(p.queues);
       if (p.view.counters) cudaFree(p.view.counters);
@@ -178,16 +192,18 @@ struct wavefront_buffers {
     return e;
   }
   cudaError_t reserve_all(int slots, int npipes) {
-    auto e = cudaMalloc(&rec, sizeof(f4) * wf_rec * (size_t)slots);
+    auto e = cudaMalloc(&rec, sizeof(f4) * wf_rec * (size_t)slots);  // 256-byte aligned
     if (e != cudaSuccess) return e;
     capacity = slots, pipes = npipes;  // from here on release() frees what exists
+    e = cudaMalloc(&vol, sizeof(f4) * wf_vol_rec * (size_t)slots);
+    if (e != cudaSuccess) return e;
     for (int i = 0; i < npipes; i++) {
       auto&  p = pipe[i];
       size_t n = (size_t)pipe_slots(slots, npipes, 0);
       e = cudaMalloc(&p.queues, sizeof(int) * 5 * n);
       if (e != cudaSuccess) return e;
       auto q = p.queues;
-      p.view.rec = rec;
+      p.view.rec = rec, p.view.vol = vol;
       p.view.queue_ext[0] = q, p.view.queue_ext[1] = q + n, p.view.queue_pdf = q + 2 * n;
       p.view.queue_shade = q + 3 * n, p.view.sort_key = q + 4 * n;
       e = cudaMalloc(&p.view.counters, sizeof(wf_counters));
@@ -208,7 +224,7 @@ struct wavefront_buffers {
 #if defined(__CUDACC__)
 
 // ---- per-slot state <-> registers -------------------------------------------
-constexpr int wf_bit_hit = 1 << 16, wf_bit_vol = 1 << 17, wf_bit_isec = 1 << 18;
+constexpr int wf_bit_hit = 1 << 16, wf_bit_vol = 1 << 17;
 constexpr int wf_bit_susp = 1 << 19;  // the slot's ray is a suspended traversal to be resumed
 
 // `store_vol`: the volume fields only change when a path enters a volume
@@ -221,10 +237,11 @@ __device__ __forceinline__ void wf_store_path(const wf_view& w, int slot, const 
   w.at(wf_rad, slot)  = {p.radiance.x, p.radiance.y, p.radiance.z, p.weight.x};
   w.at(wf_w1, slot)   = {p.weight.y, p.weight.z, p.vol_anisotropy, 0};
   if (S == shader_volpathtrace && store_vol) {
-    w.at(wf_vol0, slot) = {p.vol_density.x, p.vol_density.y, p.vol_density.z, p.vol_scattering.x};
-    w.at(wf_vol1, slot) = {p.vol_scattering.y, p.vol_scattering.z, p.vol_emission.x,
+    w.vol_at(wf_vol0, slot) = {p.vol_density.x, p.vol_density.y, p.vol_density.z,
+        p.vol_scattering.x};
+    w.vol_at(wf_vol1, slot) = {p.vol_scattering.y, p.vol_scattering.z, p.vol_emission.x,
         p.vol_emission.y};
-    w.at(wf_vol2, slot) = {p.vol_emission.z, 0, 0, 0};
+    w.vol_at(wf_vol2, slot) = {p.vol_emission.z, 0, 0, 0};
   }
 }
 
@@ -243,7 +260,7 @@ __device__ __forceinline__ void wf_load_path(const wf_view& w, int slot, path_t&
   p.vol_anisotropy = a3.z;
   p.vol_density = p.vol_scattering = p.vol_emission = {0, 0, 0};
   if (S == shader_volpathtrace && p.in_volume) {
-    auto v0 = w.at(wf_vol0, slot), v1 = w.at(wf_vol1, slot), v2 = w.at(wf_vol2, slot);
+    auto v0 = w.vol_at(wf_vol0, slot), v1 = w.vol_at(wf_vol1, slot), v2 = w.vol_at(wf_vol2, slot);
     p.vol_density = {v0.x, v0.y, v0.z}, p.vol_scattering = {v0.w, v1.x, v1.y};
     p.vol_emission = {v1.z, v1.w, v2.x};
   }
@@ -443,9 +460,8 @@ __global__ void __launch_bounds__(wf_block)
   path_t  p;
   p.o = {a0.x, a0.y, a0.z}, p.d = {a0.w, a1.x, a1.y};
   auto isec  = find_hit<S>(sc, prm, p, st);
-  w.at(wf_hit, slot)    = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
-  w.at(wf_w1, slot).w   = isec.distance;
-  w.at(wf_ray1, slot).z = i2f((f2i(a1.z) & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
+  w.at(wf_hit, slot)  = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
+  w.at(wf_hit1, slot) = {isec.distance, i2f(isec.hit ? 1 : 0), 0, 0};
   // shade class and the rank inside it
   int cls = 0;
   if (isec.hit) {
@@ -486,10 +502,6 @@ constexpr int wf_refill_sdf = 4;             // sphere tracing (B200: 07_sdfunct
 #define VPT_WF_SUSPEND_AT 20
 #endif
 constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in place)
-#if !defined(VPT_WF_LEAF_HOLD)
-#define VPT_WF_LEAF_HOLD 0
-#endif
-constexpr int wf_leaf_hold = VPT_WF_LEAF_HOLD;  // 0: test a leaf in the round that reaches it
 #if !defined(VPT_WF_SDF_STEPS)
 #define VPT_WF_SDF_STEPS 4
 #endif
@@ -497,8 +509,7 @@ constexpr int wf_sdf_steps = VPT_WF_SDF_STEPS;
 
 template <int S>
 __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
-    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at,
-        int leaf_hold) {
+    k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
   extern __shared__ int stack_mem[];
 #if defined(VPT_WF_COOP_LEAVES)
   __shared__ unsigned char leaf_tab[wf_block / 32][32 * 8];
@@ -532,12 +543,10 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
 #endif
   t.cur       = 0;
   sp.finished = true;
-  // Leaf postponement: a lane that reaches a mesh leaf HOLDS it (pops nothing more) until at
-  // least `leaf_hold` lanes of the warp hold one or no lane can descend any further; then all
-  // of them run the primitive tests together. ncu r01c: the (long) leaf code ran at ~5 of 32
-  // lanes when every round ended with the tests of whoever had found a leaf. A ray's own
-  // sequence of operations is unchanged (it does nothing between finding and testing a leaf).
-  int held = 0;
+  // (Leaf postponement - a lane holds the leaf it reached until >= N lanes of the warp hold
+  // one - was measured on B200 and dropped: with <= 8 pops per round nearly every walking lane
+  // ends its round on a leaf anyway, so N = 4 ... 28 changed neither the instruction count
+  // (145.0 M vs 144.7-145.2 M per launch, profiles/r02a_*) nor the step time (180.5 ms).)
   while (running) {
     unsigned idle = __ballot_sync(full, !has_ray);
     if (more && (__popc(idle) >= (sdf ? wf_refill_sdf : wf_refill))) {
@@ -574,23 +583,14 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
         if (has_ray && !sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
     } else {
 #if !defined(VPT_WF_COOP_LEAVES)
-      bool moving = has_ray && held == 0 && !t.done();
-      if (moving) held = t.descend(sc, ray, st);
-      unsigned holders = __ballot_sync(full, held != 0);
-      if (holders) {
-        unsigned movers = __ballot_sync(full, has_ray && held == 0 && !t.done());
-        if (__popc(holders) >= leaf_hold || movers == 0) {
-          if (held != 0) t.test_leaf(sc, held);
-          held = 0;
-        }
-      }
+      if (has_ray && !t.done()) t.round(sc, ray, st);
 #else
       int leaf = 0;
       if (has_ray && !t.done()) leaf = t.descend(sc, ray, st);
       wf_test_leaves_warp(sc, t, leaf, leaf_tab[threadIdx.x >> 5]);
 #endif
     }
-    bool     retire   = has_ray && (sdf ? sp.done() : (held == 0 && t.done()));
+    bool     retire   = has_ray && (sdf ? sp.done() : t.done());
     unsigned retiring = __ballot_sync(full, retire);
     if (retire) {
       isect_t isec;
@@ -598,9 +598,10 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
         isec = {sp.r.hit, sp.r.instance, sp.r.sdf, {0, 0}, sp.r.dist};
       else
         isec = {t.h.hit, t.h.instance, t.h.element, t.h.uv, t.h.distance};
-      w.at(wf_hit, slot)    = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
-      w.at(wf_w1, slot).w   = isec.distance;
-      w.at(wf_ray1, slot).z = i2f((flags & ~wf_bit_isec) | (isec.hit ? wf_bit_isec : 0));
+      w.at(wf_hit, slot)  = {i2f(isec.instance), i2f(isec.element), isec.uv.x, isec.uv.y};
+      w.at(wf_hit1, slot) = {isec.distance, i2f(isec.hit ? 1 : 0), 0, 0};
+      // (a resumed ray's park flag in sector 0 is cleared by shade, which rewrites the flags
+      // of every slot it sees before the next extend launch reads them)
       int cls = 0;
       if (isec.hit) {
         int material;
@@ -623,10 +624,7 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
     }
     unsigned walking = __ballot_sync(full, has_ray);
     if (!more && walking && __popc(walking) <= (sdf ? suspend_at : suspend_mesh)) {
-      if constexpr (!sdf) {
-        if (held != 0) t.test_leaf(sc, held);  // a parked walk carries no held leaf
-        held = 0;
-      }
+
       // park what is left of this warp for the next iteration's launch
       int n = __popc(walking), leader = __ffs(walking) - 1;
       int rank = __popc(walking & ((1u << lane) - 1));
@@ -703,9 +701,8 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
     path_t p;
     int    remaining;
     wf_load_path<S>(w, slot, p, remaining);
-    auto a4   = w.at(wf_hit, slot);
-    auto isec = isect_t{(f2i(w.at(wf_ray1, slot).z) & wf_bit_isec) != 0, f2i(a4.x), f2i(a4.y),
-        {a4.z, a4.w}, w.at(wf_w1, slot).w};
+    auto a4 = w.at(wf_hit, slot), a5 = w.at(wf_hit1, slot);
+    auto isec = isect_t{f2i(a5.y) != 0, f2i(a4.x), f2i(a4.y), {a4.z, a4.w}, a5.x};
     auto      rng     = wf_load_rng(w, slot);
     bool      was_vol = p.in_volume;
     pending_t pd;
@@ -727,30 +724,49 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
   wf_push(w.queue_pdf, &w.counters->count_pdf, to_pdf, slot);
 }
 
+// Light pdf in two kernels. k_wf_lightpdf computes sample_lights_pdf along the slot's next ray
+// (instance-targeted walks, sdf marches, environment texel pdf) and leaves the value in the
+// slot's hit field; it carries no path state, so it fits in half the registers of the fused
+// form (ncu r02a: 149 registers, 3 blocks per SM, 18 % of the warp slots, long-scoreboard
+// bound). k_wf_pdf_tail then applies the MIS weight and runs bounce_tail / path regeneration.
+#if !defined(VPT_PDF_BLOCKS)
+#define VPT_PDF_BLOCKS 6
+#endif
+template <int S>
+__global__ void __launch_bounds__(wf_block, VPT_PDF_BLOCKS)
+    k_wf_lightpdf(const DScene sc, const DParams prm, wf_view w, int cur) {
+  extern __shared__ int stack_mem[];
+  int tid   = blockIdx.x * blockDim.x + threadIdx.x;
+  int count = w.counters->count_pdf;
+  if (tid == 0) w.counters->rays_lightpdf += (unsigned long long)count;
+  if (tid >= count) return;
+  int     slot = w.queue_pdf[tid];
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
+  // after shade_hit the next ray is (position, incoming): the pdf is taken along it
+  auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
+  auto lpdf = sample_lights_pdf(sc, f3{a0.x, a0.y, a0.z}, f3{a0.w, a1.x, a1.y},
+      prm.spheretrace_maxiter, st);
+  w.at(wf_hit1, slot).z = lpdf;
+}
+
 template <int S>
 __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
-    k_wf_lightpdf(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
+    k_wf_pdf_tail(const DScene sc, const DParams prm, wf_view w, f4* __restrict__ image,
         rng_t* __restrict__ rngs, int cur) {
-  extern __shared__ int stack_mem[];
   int  tid    = blockIdx.x * blockDim.x + threadIdx.x;
   int  count  = w.counters->count_pdf;
   bool to_ext = false;
   int  slot   = 0;
-  if (tid == 0) {
-    w.counters->rays_lightpdf += (unsigned long long)count;
-    w.counters->count_ext[cur] = 0;  // consumed; the next iteration fills it
-  }
+  if (tid == 0) w.counters->count_ext[cur] = 0;  // consumed; the next iteration fills it
   if (tid < count) {
     slot    = w.queue_pdf[tid];
     int idx = tile_pixel_index(slot, prm.width, prm.height);
-    stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
     path_t  p;
     int     remaining;
     wf_load_path<S>(w, slot, p, remaining);
-    auto a5 = w.at(wf_mis, slot);
-    auto pd = pending_t{p.o, p.d, {a5.x, a5.y, a5.z}, a5.w};
-    // after shade_hit the next ray is (position, incoming): the pdf is taken along it
-    auto lpdf = sample_lights_pdf(sc, p.o, p.d, prm.spheretrace_maxiter, st);
+    auto a5   = w.at(wf_mis, slot);
+    auto pd   = pending_t{p.o, p.d, {a5.x, a5.y, a5.z}, a5.w};
+    auto lpdf = w.at(wf_hit1, slot).z;
     apply_lightpdf(p, pd, lpdf);
     auto rng   = wf_load_rng(w, slot);
     bool alive = bounce_tail<S>(prm, p, rng);
@@ -929,9 +945,6 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   // lanes still walking at or below which a warp parks its rays once the queue is empty
   const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
-  // lanes that must hold a leaf before the warp runs the primitive tests (see the kernel)
-  const char* hold_env = getenv("VPT_WF_LEAF_HOLD");
-  int leaf_hold = hold_env ? atoi(hold_env) : wf_leaf_hold;
   // parked BVH walks need record pools (sphere tracing parks into the slot record itself)
 #if defined(VPT_WF_SUSPEND_MESH)
   if (persistent && !is_sdf_shader<S>()) {
@@ -973,7 +986,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (trace) trace->mark(grid);
       if (persistent)
         k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
-            scene.d, prm, w, p.cur, suspend_at, leaf_hold);
+            scene.d, prm, w, p.cur, suspend_at);
       else
         k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
       if (it == 0 && timed) cudaEventRecord(wf.k1, p.stream);
@@ -981,10 +994,11 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (trace) trace->mark(grid);
       k_wf_shade<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
       if (trace) trace->mark(grid);
-      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
+      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+      k_wf_pdf_tail<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
       if (trace) trace->mark(grid);
       p.cur ^= 1;
-      *launches += 4;
+      *launches += 5;
     }
     if (timed) timed_pending = true, timed_active = p.active, timed_batch = p.batches;
     int  k = p.batches & 1;
