@@ -128,3 +128,243 @@ std::vector<sdf_typed> read_sdf_params(const std::string& filename, const scene_
   return result;
 }
 
+// Everything the C ABI takes, as pointers into the caller's own vectors: vec3f / vec2f / vec4f /
+// vec3i / vec4i / frame3f are plain float / int arrays and bvh_node is byte-compatible with
+// vpt_bvh_node, so nothing is copied except the small per-object structs.
+struct desc_storage {
+  std::vector<vpt_camera_desc>          cameras;
+  std::vector<vpt_instance_desc>        instances;
+  std::vector<vpt_shape_desc>           shapes;
+  std::vector<vpt_material_desc>        materials;
+  std::vector<vpt_texture_desc>         textures;
+  std::vector<vpt_environment_desc>     environments;
+  std::vector<vpt_volume_desc>          volumes;
+  std::vector<vpt_volume_instance_desc> vol_instances;
+  std::vector<vpt_sdf_desc>             sdfs;
+  std::vector<vpt_light_desc>           lights;
+  std::vector<vpt_bvh_desc>             shape_bvhs;
+  vpt_scene_desc                        desc{};
+};
+
+vpt_bvh_desc describe_bvh(const bvh_data& bvh) {
+  return {(const vpt_bvh_node*)bvh.nodes.data(), (int32_t)bvh.nodes.size(), bvh.primitives.data(),
+      (int32_t)bvh.primitives.size()};
+}
+
+void describe(desc_storage& s, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, const std::vector<sdf_typed>& typed) {
+  if (bvh.embree_bvh) throw std::runtime_error("Embree BVHs have no node array to upload");
+  if (bvh.shapes.size() != scene.shapes.size())
+    throw std::runtime_error("bvh does not match the scene");
+  for (auto& c : scene.cameras) {
+    auto d = vpt_camera_desc{};
+    memcpy(d.frame, &c.frame, 48);
+    d.orthographic = c.orthographic ? 1 : 0;
+    d.lens = c.lens, d.film = c.film, d.aspect = c.aspect, d.focus = c.focus, d.aperture = c.aperture;
+    s.cameras.push_back(d);
+  }
+  for (auto& i : scene.instances) {
+    auto d = vpt_instance_desc{};
+    memcpy(d.frame, &i.frame, 48);
+    d.shape = i.shape, d.material = i.material;
+    s.instances.push_back(d);
+  }
+  for (auto& sh : scene.shapes) {
+    auto d = vpt_shape_desc{};
+    d.positions = (const float*)sh.positions.data(), d.num_positions = (int)sh.positions.size();
+    d.normals = sh.normals.empty() ? nullptr : (const float*)sh.normals.data();
+    d.num_normals = (int)sh.normals.size();
+    d.texcoords = sh.texcoords.empty() ? nullptr : (const float*)sh.texcoords.data();
+    d.num_texcoords = (int)sh.texcoords.size();
+    d.colors = sh.colors.empty() ? nullptr : (const float*)sh.colors.data();
+    d.num_colors = (int)sh.colors.size();
+    d.triangles = (const int32_t*)sh.triangles.data(), d.num_triangles = (int)sh.triangles.size();
+    d.quads = (const int32_t*)sh.quads.data(), d.num_quads = (int)sh.quads.size();
+    d.num_points = (int)sh.points.size(), d.num_lines = (int)sh.lines.size();
+    s.shapes.push_back(d);
+  }
+  for (auto& m : scene.materials) {
+    auto d = vpt_material_desc{};
+    d.type = (int)m.type;
+    memcpy(d.emission, &m.emission, 12), memcpy(d.color, &m.color, 12);
+    d.roughness = m.roughness, d.metallic = m.metallic, d.ior = m.ior;
+    memcpy(d.scattering, &m.scattering, 12);
+    d.scanisotropy = m.scanisotropy, d.trdepth = m.trdepth, d.opacity = m.opacity;
+    d.emission_tex = m.emission_tex, d.color_tex = m.color_tex, d.roughness_tex = m.roughness_tex;
+    d.scattering_tex = m.scattering_tex, d.normal_tex = m.normal_tex;
+    s.materials.push_back(d);
+  }
+  for (auto& t : scene.textures)
+    s.textures.push_back({t.width, t.height, t.linear ? 1 : 0,
+        t.pixelsf.empty() ? nullptr : (const float*)t.pixelsf.data(),
+        t.pixelsb.empty() ? nullptr : (const uint8_t*)t.pixelsb.data()});
+  for (auto& e : scene.environments) {
+    auto d = vpt_environment_desc{};
+    memcpy(d.frame, &e.frame, 48), memcpy(d.emission, &e.emission, 12);
+    d.emission_tex = e.emission_tex;
+    s.environments.push_back(d);
+  }
+  for (auto& v : scene.volumes)
+    s.volumes.push_back({{v.whd.x, v.whd.y, v.whd.z}, v.res, v.vol.data()});
+  for (auto& v : scene.vol_instances) {
+    auto d = vpt_volume_instance_desc{};
+    memcpy(d.frame, &v.frame, 48);
+    d.scalef = v.scalef, d.volume = v.volume, d.material = v.material;
+    s.vol_instances.push_back(d);
+  }
+  for (size_t i = 0; i < scene.sdfs.size(); i++) {
+    auto d = vpt_sdf_desc{};
+    memcpy(d.frame, &scene.sdfs[i].frame, 48);
+    d.type = typed[i].type, d.material = scene.sdfs[i].material;
+    memcpy(d.params, typed[i].params, 16), memcpy(d.whd, typed[i].whd, 12);
+    s.sdfs.push_back(d);
+  }
+  for (auto& l : lights.lights)
+    s.lights.push_back({l.instance, l.environment, l.sdf, l.elements_cdf.data(),
+        (int32_t)l.elements_cdf.size()});
+  for (auto& b : bvh.shapes) s.shape_bvhs.push_back(describe_bvh(b));
+  auto& d = s.desc;
+  d.num_cameras = (int)s.cameras.size(), d.cameras = s.cameras.data();
+  d.num_instances = (int)s.instances.size(), d.instances = s.instances.data();
+  d.num_shapes = (int)s.shapes.size(), d.shapes = s.shapes.data();
+  d.num_materials = (int)s.materials.size(), d.materials = s.materials.data();
+  d.num_textures = (int)s.textures.size(), d.textures = s.textures.data();
+  d.num_environments = (int)s.environments.size(), d.environments = s.environments.data();
+  d.num_volumes = (int)s.volumes.size(), d.volumes = s.volumes.data();
+  d.num_vol_instances = (int)s.vol_instances.size(), d.vol_instances = s.vol_instances.data();
+  d.num_sdfs = (int)s.sdfs.size(), d.sdfs = s.sdfs.data();
+  d.num_lights = (int)s.lights.size(), d.lights = s.lights.data();
+  d.scene_bvh = describe_bvh(bvh), d.shape_bvhs = s.shape_bvhs.data();
+}
+
+// Device mirrors, keyed by the caller's objects (the reference's structs are not ours to extend):
+// one uploaded scene and one device state per pathtrace_state.
+struct device_binding {
+  vpt_scene*        scene = nullptr;
+  vpt_state*        state = nullptr;
+  const scene_data* scene_key = nullptr;
+  const bvh_scene*  bvh_key = nullptr;
+  ~device_binding() {
+    if (state) vpt_cuda_free_state(state);
+    if (scene) vpt_cuda_free_scene(scene);
+  }
+};
+std::unordered_map<const pathtrace_state*, std::unique_ptr<device_binding>> g_bindings;
+
+device_binding& binding_of(const pathtrace_state& state) {
+  auto& slot = g_bindings[&state];
+  if (!slot) slot = std::make_unique<device_binding>();
+  return *slot;
+}
+
+}  // namespace
+
+void pathtrace_cuda_scene_file(const std::string& filename) {
+  auto lock         = std::lock_guard{g_mutex};
+  g_scene_file      = filename;
+  g_sdf_cache_scene = nullptr;
+}
+
+void pathtrace_cuda_release(const pathtrace_state& state) {
+  auto lock = std::lock_guard{g_mutex};
+  g_bindings.erase(&state);
+}
+
+// Progressively computes an image: one sample per call, as yocto_pathtrace.cpp:1052-1092.
+// The accumulation image and the per-pixel generators live on the device between calls;
+// state.samples is kept, state.image / state.hits / state.rngs are refreshed by get_render
+// (image) or pathtrace_cuda_sync (all three), not per sample.
+void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, const pathtrace_params& params) {
+  if (state.samples >= params.samples) return;  // :1055
+  auto  lock = std::lock_guard{g_mutex};
+  auto& dev  = binding_of(state);
+  // the state is being reused with another scene: drop the mirrors
+  if (dev.scene && (dev.scene_key != &scene || dev.bvh_key != &bvh)) g_bindings.erase(&state);
+  pathtrace_samples_unlocked(state, scene, bvh, lights, params);
+}
+
+void pathtrace_samples_unlocked(pathtrace_state& state, const scene_data& scene,
+    const bvh_scene& bvh, const pathtrace_lights& lights, const pathtrace_params& params) {
+  auto& dev = binding_of(state);
+  if (!dev.scene) {
+    if (g_sdf_cache_scene != &scene) {
+      g_sdf_cache       = read_sdf_params(g_scene_file, scene);
+      g_sdf_cache_scene = &scene;
+    }
+    auto storage = desc_storage{};
+    describe(storage, scene, bvh, lights, g_sdf_cache);
+    throw_on(vpt_cuda_upload_scene(&storage.desc, &dev.scene));
+    dev.scene_key = &scene, dev.bvh_key = &bvh;
+  }
+  if (!dev.state || state.samples == 0) {
+    // a fresh (or reset) pathtrace_state: its generators are make_state's (:975-978)
+    if ((int)state.rngs.size() != state.width * state.height)
+      throw std::invalid_argument{"state should come from make_state"};
+    if (!dev.state)
+      throw_on(vpt_cuda_create_state(state.width, state.height,
+          (const uint64_t*)state.rngs.data(), &dev.state));
+    else
+      throw_on(vpt_cuda_reset_state(dev.state, (const uint64_t*)state.rngs.data()));
+  }
+  auto p                = vpt_params{};
+  p.camera              = params.camera;
+  p.resolution          = params.resolution;
+  p.shader              = (int)params.shader;
+  p.samples             = params.samples;
+  p.bounces             = params.bounces;
+  p.noparallel          = params.noparallel ? 1 : 0;
+  p.pratio              = params.pratio;
+  p.exposure            = params.exposure;
+  p.filmic              = params.filmic ? 1 : 0;
+  p.noimplicit_mis      = params.noimplicit_mis ? 1 : 0;
+  p.spheretrace_maxiter = params.spheretrace_maxiter;
+  p.pipeline            = VPT_PIPELINE_AUTO;
+  throw_on(vpt_cuda_trace_samples(dev.scene, dev.state, &p, 1));  // get_shader's throw: :948
+  state.samples += 1;
+}
+
+// Copies the device sums, hit counts and generators back into the caller's pathtrace_state
+// (what the reference's loop leaves there after every sample).
+void pathtrace_cuda_sync(pathtrace_state& state) {
+  auto lock = std::lock_guard{g_mutex};
+  auto it   = g_bindings.find(&state);
+  if (it == g_bindings.end() || !it->second->state) return;
+  auto n = (size_t)state.width * state.height;
+  state.image.resize(n), state.hits.resize(n), state.rngs.resize(n);
+  throw_on(vpt_cuda_download_image(it->second->state, &state.image[0].x, n * 4));
+  throw_on(vpt_cuda_download_rngs(it->second->state, (uint64_t*)state.rngs.data(), n * 2));
+  for (auto& h : state.hits) h = state.samples;  // hits[idx] += 1 per sample (:1089), never read
+}
+
+static void check_image(const color_image& image, int width, int height, bool linear) {
+  if (image.width != width || image.height != height)
+    throw std::invalid_argument{"image should have the same size"};
+  if (image.linear != linear)
+    throw std::invalid_argument{linear ? "expected linear image" : "expected srgb image"};
+}
+
+// Get resulting render (yocto_pathtrace.cpp:1105-1116): sums * (1 / samples)
+color_image get_render(const pathtrace_state& state) {
+  auto image = make_image(state.width, state.height, true);
+  get_render(image, state);
+  return image;
+}
+void get_render(color_image& image, const pathtrace_state& state) {
+  check_image(image, state.width, state.height, true);
+  auto lock  = std::lock_guard{g_mutex};
+  auto it    = g_bindings.find(&state);
+  auto scale = 1.0f / (float)state.samples;
+  if (it == g_bindings.end() || !it->second->state) {
+    // nothing traced on the device yet: the host sums are the state
+    for (auto idx = 0; idx < state.width * state.height; idx++)
+      image.pixels[idx] = state.image[idx] * scale;
+    return;
+  }
+  auto sums = std::vector<vec4f>((size_t)state.width * state.height);
+  throw_on(vpt_cuda_download_image(it->second->state, &sums[0].x, sums.size() * 4));
+  for (auto idx = 0; idx < state.width * state.height; idx++)
+    image.pixels[idx] = sums[idx] * scale;
+}
+
+}  // namespace yocto

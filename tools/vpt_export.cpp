@@ -1,4 +1,7 @@
-// vpt_export — TEST/ASSET TOOLING (oracle side). Loads a scene with the
+// vpt_export — the product's scene-input tool: JSON / glTF / OBJ / PLY scene -> .vptscene, the
+// archive `ypathtrace` and the bindings read. Scene loading is outside the hot path:
+// it is done by the reference's own loaders, so this tool is compiled against the reference
+// (oracle/Makefile builds it where /root/reference exists). Loads a scene with the
 // reference's own loaders (load_scene, yocto_sceneio.cpp:2676; JSON 3544),
 // runs the reference's host-side tesselate_surfaces (yocto_pathtrace.cpp:1275)
 // and writes the result as a ".vptscene" named-array archive

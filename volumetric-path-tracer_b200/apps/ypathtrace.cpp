@@ -2,10 +2,10 @@
 //
 // Mirrors run() / run_offline() of the reference CLI
 // (apps/ypathtrace/ypathtrace.cpp:41-87, :307-341): same flags, defaults and
-// call sequence (load_scene -> tesselate_surfaces -> make_bvh -> make_lights ->
+// call sequence (load_scene [already tessellated, tools/vpt_export] -> make_bvh -> make_lights ->
 // make_state -> pathtrace_samples x N -> get_render -> save_image). Differences:
 // the scene is a ".vptscene" archive (asset loading stays with the reference's
-// loaders, see oracle/tools/vpt_export.cpp); --interactive is unavailable on
+// loaders, see tools/vpt_export.cpp); --interactive is unavailable on
 // this box (no OpenGL); the image writers are .hdr / .pfm / .ppm / .png.
 // Added flags: --pipeline {auto,mega,wavefront}, --batch N, --device K, --device-lights
 // (make_lights on the GPU).
@@ -211,7 +211,6 @@ int main(int argc, const char** argv) {
     auto scene = scene_data{};
     if (!load_scene(scenename, scene, error)) print_fatal(error);
     printf("load scene: %.3f s\n", since(t0));
-    tesselate_surfaces(scene);
     t0       = clock();
     auto bvh = make_bvh(scene, params);
     printf("build bvh: %.3f s\n", since(t0));

@@ -128,8 +128,6 @@ pathtrace_lights make_lights(const scene_data& scene, const pathtrace_params& pa
   return lights;
 }
 
-void tesselate_surfaces(scene_data&) {}
-
 // ---------------------------------------------------------------------------
 // device binding
 // ---------------------------------------------------------------------------

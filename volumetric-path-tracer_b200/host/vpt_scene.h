@@ -133,7 +133,7 @@ struct bvh_data {
 using bvh_scene = bvh_data;
 using bvh_shape = bvh_data;
 
-// Loads a ".vptscene" archive written by oracle/tools/vpt_export or by the
+// Loads a ".vptscene" archive written by tools/vpt_export or by the
 // Python fixture generators (volumetric-path-tracer_b200/archive.py).
 bool load_scene(const std::string& filename, scene_data& scene, std::string& error);
 

@@ -1,5 +1,5 @@
 // vpt_sceneio.cpp — ".vptscene" archive -> vpt::scene_data.
-// Array names and layouts are the ones oracle/tools/vpt_export.cpp writes from
+// Array names and layouts are the ones tools/vpt_export.cpp writes from
 // the reference's scene_data and archive.py writes from numpy fixtures.
 #include "vpt_archive.h"
 #include "vpt_scene.h"
