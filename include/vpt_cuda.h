@@ -284,6 +284,24 @@ int  vpt_cuda_import_image(vpt_state* state, const void* device_src, size_t n);
  * ids: [n][3] = hit, instance, element; uvd: [n][3] = u, v, distance. */
 int  vpt_cuda_intersect(vpt_scene* scene, const float* rays, int n, int instance,
          int32_t* ids, float* uvd);
+/* vpt_cuda_intersect for callers that cannot allocate. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that must not call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it). Same arguments and results as
+ * vpt_cuda_intersect (host pointers in, host pointers out, blocking), but the device staging of
+ * rays / ids / uvd is one static __device__ array inside the library instead of three
+ * cudaMalloc'ed buffers: the call performs no cudaMalloc / cudaFree / allocating library call.
+ *   - limit: n <= VPT_NOALLOC_MAX_RAYS (65 536 rays = 3.5 MiB of device memory, held by every
+ *     GPU that loads the library until the process exits); larger n -> VPT_ERR_INVALID with a
+ *     message, nothing is launched;
+ *   - the scene must live on the CURRENT device (the array's address is taken per device with
+ *     cudaGetSymbolAddress on first use);
+ *   - every call shares the array and finds the last call's contents in it (all n records are
+ *     overwritten, nothing needs clearing); calls that overlap on the GPU would race: host
+ *     threads of one process are serialised inside the call, separate processes have separate
+ *     copies. */
+#define VPT_NOALLOC_MAX_RAYS 65536
+int  vpt_cuda_intersect_noalloc(vpt_scene* scene, const float* rays, int n, int instance,
+         int32_t* ids, float* uvd);
 /* ids: [n][3] = hit, vol_instance, sdf; dn: [n][4] = distance, normal.xyz */
 int  vpt_cuda_spheretrace(vpt_scene* scene, const float* rays, int n, int maxiter,
          int32_t* ids, float* dn);

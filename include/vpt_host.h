@@ -64,6 +64,9 @@ void* vpth_render_device_image(vpth_render* render);
 int  vpth_render_export_image(vpth_render* render, void* device_dst);
 int  vpth_render_import_image(vpth_render* render, const void* device_src, int total_samples);
 
+/* the vpt_scene handle of include/vpt_cuda.h behind a host scene (uploads it on first use), for
+ * callers / tests that talk to libvpt_cuda.so directly; owned by `scene`; null on failure */
+vpt_scene* vpth_scene_device_handle(vpth_scene* scene);
 int  vpth_intersect(vpth_scene* scene, const float* rays, int n, int instance, int32_t* ids,
          float* uvd);
 int  vpth_spheretrace(vpth_scene* scene, const float* rays, int n, int maxiter, int32_t* ids,

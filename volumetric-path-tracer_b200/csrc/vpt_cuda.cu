@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -655,6 +656,94 @@ int vpt_cuda_intersect(vpt_scene* scene, const float* rays, int n, int instance,
   if (e == cudaSuccess) e = cudaMemcpy(uvd, d_uvd, (size_t)n * 3 * sizeof(float), cudaMemcpyDeviceToHost);
   cudaFree(d_rays), cudaFree(d_ids), cudaFree(d_uvd);
   if (e != cudaSuccess) return cuda_fail(e, "vpt_cuda_intersect");
+  return VPT_OK;
+}
+
+}  // extern "C" (the scratch array and its kernel have C++ linkage)
+
+// ---- first-hit queries without any allocation -------------------------------------------------
+// vpt_cuda_intersect stages its ray batch and results in three cudaMalloc'ed buffers per call.
+// Some callers cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc): this variant stages through ONE file-scope device array instead.
+// Every GPU that loads the library holds the array until the process exits.
+//   * the array name is a host-side stand-in in host code, NOT a device address: the address
+//     comes from cudaGetSymbolAddress, once per device, with that device current;
+//   * all calls share the array: the kernel overwrites every record of [0, n) it is asked for
+//     and nothing has to start at zero, but two calls that overlap on the GPU would race, so the
+//     entry point serialises host threads of this process (it is blocking anyway).
+constexpr int      noalloc_max_rays  = VPT_NOALLOC_MAX_RAYS;
+constexpr size_t   noalloc_ray_bytes = 8 * sizeof(float), noalloc_ids_bytes = 3 * sizeof(int),
+                   noalloc_uvd_bytes = 3 * sizeof(float);
+constexpr size_t   noalloc_bytes =
+    (size_t)noalloc_max_rays * (noalloc_ray_bytes + noalloc_ids_bytes + noalloc_uvd_bytes);
+static __device__ __align__(256) unsigned char g_noalloc_scratch[noalloc_bytes];  // 3.5 MiB
+
+// the scratch variant of k_intersect: {rays | ids | uvd} regions of one array, sized for
+// noalloc_max_rays whatever n is, so region offsets never depend on the call
+__global__ void __launch_bounds__(mega_block)
+    k_intersect_scratch(const DScene sc, unsigned char* __restrict__ scratch, int n, int instance) {
+  extern __shared__ int stack_mem[];
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  auto rays = reinterpret_cast<const float*>(scratch);
+  auto ids  = reinterpret_cast<int*>(scratch + (size_t)noalloc_max_rays * noalloc_ray_bytes);
+  auto uvd  = reinterpret_cast<float*>(
+      scratch + (size_t)noalloc_max_rays * (noalloc_ray_bytes + noalloc_ids_bytes));
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
+  auto    r   = rays + 8 * (size_t)i;
+  auto    ray = ray3{{r[0], r[1], r[2]}, {r[3], r[4], r[5]}, r[6], r[7]};
+  auto    h   = instance >= 0 ? intersect_instance(sc, instance, ray, st)
+                              : intersect_scene(sc, ray, st);
+  ids[3 * i + 0] = h.hit ? 1 : 0;
+  ids[3 * i + 1] = h.hit ? h.instance : -1;
+  ids[3 * i + 2] = h.hit ? h.element : -1;
+  uvd[3 * i + 0] = h.hit ? h.uv.x : 0;
+  uvd[3 * i + 1] = h.hit ? h.uv.y : 0;
+  uvd[3 * i + 2] = h.hit ? h.distance : 0;
+}
+
+static std::mutex     g_noalloc_mutex;
+static unsigned char* g_noalloc_ptr[64] = {};  // device address of the array, per device
+
+extern "C" {
+
+int vpt_cuda_intersect_noalloc(vpt_scene* scene, const float* rays, int n, int instance,
+    int32_t* ids, float* uvd) {
+  if (!scene || !rays || !ids || !uvd || n < 0) return set_error(VPT_ERR_INVALID, "bad argument");
+  if (instance >= scene->flat.d.num_instances)
+    return set_error(VPT_ERR_INVALID, "instance out of range");
+  if (n > noalloc_max_rays)
+    return set_error(VPT_ERR_INVALID, "vpt_cuda_intersect_noalloc: " + std::to_string(n) +
+                                          " rays exceed the static scratch of " +
+                                          std::to_string(noalloc_max_rays) +
+                                          " rays (split the batch or use vpt_cuda_intersect)");
+  if (n == 0) return VPT_OK;
+  auto lock   = std::lock_guard<std::mutex>(g_noalloc_mutex);
+  int  device = 0;
+  VPT_CUDA_TRY(cudaGetDevice(&device));
+  if (device < 0 || device >= 64) return set_error(VPT_ERR_UNSUPPORTED, "device index above 63");
+  if (device != scene->device)
+    return set_error(VPT_ERR_INVALID, "the scene lives on another device than the current one");
+  if (!g_noalloc_ptr[device]) {
+    // set-up, once per device, with that device current
+    void* ptr = nullptr;
+    VPT_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    if (!ptr) return set_error(VPT_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[device] = static_cast<unsigned char*>(ptr);
+  }
+  auto   base  = g_noalloc_ptr[device];
+  auto   d_ids = base + (size_t)noalloc_max_rays * noalloc_ray_bytes;
+  auto   d_uvd = base + (size_t)noalloc_max_rays * (noalloc_ray_bytes + noalloc_ids_bytes);
+  size_t smem  = (size_t)scene->flat.stack_depth * vpt_stack_words * mega_block * sizeof(int);
+  if (smem > 48 * 1024)
+    VPT_CUDA_TRY(cudaFuncSetAttribute(k_intersect_scratch,
+        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  VPT_CUDA_TRY(cudaMemcpy(base, rays, (size_t)n * noalloc_ray_bytes, cudaMemcpyHostToDevice));
+  k_intersect_scratch<<<(n + mega_block - 1) / mega_block, mega_block, smem>>>(scene->flat.d, base,
+      n, instance);
+  VPT_CUDA_TRY(cudaGetLastError());
+  VPT_CUDA_TRY(cudaMemcpy(ids, d_ids, (size_t)n * noalloc_ids_bytes, cudaMemcpyDeviceToHost));
+  VPT_CUDA_TRY(cudaMemcpy(uvd, d_uvd, (size_t)n * noalloc_uvd_bytes, cudaMemcpyDeviceToHost));
   return VPT_OK;
 }
 

@@ -310,6 +310,16 @@ int vpth_render_import_image(vpth_render* r, const void* device_src, int total_s
   });
 }
 
+vpt_scene* vpth_scene_device_handle(vpth_scene* scene) {
+  if (!scene) return nullptr;
+  try {
+    return device_scene_of(scene);
+  } catch (const std::exception& e) {
+    g_error = e.what();
+    return nullptr;
+  }
+}
+
 int vpth_intersect(vpth_scene* s, const float* rays, int n, int instance, int32_t* ids,
     float* uvd) {
   if (!s) return VPT_ERR_INVALID;
