@@ -225,6 +225,7 @@ typedef struct vpt_trace_stats {
 
 int  vpt_cuda_device_count(void);
 int  vpt_cuda_set_device(int device);
+int  vpt_cuda_current_device(void); /* of the calling thread; -1 without a device */
 const char* vpt_cuda_last_error(void);
 
 /* page-lock caller-owned host buffers so uploads / downloads run at full PCIe rate */
@@ -269,7 +270,29 @@ int  vpt_cuda_get_trace_stats(const vpt_state* state, vpt_trace_stats* stats);
  * the total over ranks). A quarter of the float image crosses PCIe; bytes equal the reference's. */
 int  vpt_cuda_download_srgb8(vpt_state* state, int samples, uint8_t* rgba, size_t n);
 
-/* un-normalised sums, n = width*height*4 floats (get_render divides by samples) */
+/* The same with the reference's display tonemap in front (tonemap(), yocto_color.h:306-316, driven by
+ * pathtrace_params.exposure / .filmic, yocto_pathtrace.h:94-95, as the viewer's display loop does,
+ * apps/ypathtrace/ypathtrace.cpp:159-189): rgb * exp2(exposure) if exposure != 0, the ACES-fitted
+ * tonemap_filmic curve (yocto_color.h:274-281) if filmic, then rgb_to_srgb + float_to_byte.
+ * Bytes equal the reference's. The device and pinned host buffers live with the state (no
+ * allocation per frame of a progressive preview). */
+int  vpt_cuda_download_tonemapped8(vpt_state* state, int samples, float exposure, int filmic,
+         uint8_t* rgba, size_t n);
+
+/* Multi-GPU accumulation (the sample loop of apps/ypathtrace/ypathtrace.cpp:77-81
+ * is where it lands): `peer` - a state of the same size, normally on another device, rendering a
+ * disjoint sample range of every pixel (vpt_cuda_advance_rngs) - joins `root`. From then on
+ * vpt_cuda_download_image / _srgb8 / _tonemapped8 on `root` return the SUM of the root's and all
+ * peers' accumulation images: one kernel on the root's device reads the peers' images through
+ * P2P loads over NVLink (copied over first where P2P is unavailable); the root's own image is
+ * not modified. Peers must outlive the root's downloads; remove_peers detaches them. */
+int  vpt_cuda_state_add_peer(vpt_state* root, vpt_state* peer);
+int  vpt_cuda_state_remove_peers(vpt_state* root);
+/* samples of the root plus all peers: the divisor of the summed image */
+int  vpt_cuda_state_total_samples(const vpt_state* state);
+
+/* un-normalised sums, n = width*height*4 floats (get_render divides by samples); with peers:
+ * the sum over root and peers (see vpt_cuda_state_add_peer) */
 int  vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n);
 int  vpt_cuda_download_rngs(vpt_state* state, uint64_t* rngs, size_t n);
 /* device pointer of the accumulation image, for a collective on the caller's side */

@@ -57,6 +57,11 @@ int  vpth_render_done_samples(const vpth_render* render);
 int  vpth_render_get_image(vpth_render* render, float* rgba, int normalized);
 /* device-side output stage: 8-bit sRGB RGBA of the current render, [height][width][4] */
 int  vpth_render_get_srgb8(vpth_render* render, uint8_t* rgba);
+/* get_render + tonemap(exposure, filmic) + 8 bit on the device (vpt_cuda_download_tonemapped8) */
+int  vpth_render_get_tonemapped8(vpth_render* render, float exposure, int filmic, uint8_t* rgba);
+/* render on `gpus` GPUs of this box from the next vpth_render_samples call on (pathtrace_params.gpus
+ * of host/vpt_pathtrace.h: sample-range sharding, the sum happens inside get_image / get_srgb8) */
+int  vpth_render_set_gpus(vpth_render* render, int gpus);
 int  vpth_render_stats(const vpth_render* render, vpt_trace_stats* stats);
 /* device pointer of the accumulation image (for a collective), or null */
 void* vpth_render_device_image(vpth_render* render);

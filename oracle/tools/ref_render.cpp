@@ -222,6 +222,16 @@ int main(int argc, const char** argv) {
       rgb_to_srgb(ldr, image.pixels);
       out.add("image_srgb8", vpt::dt_u8, {(uint64_t)state.height, (uint64_t)state.width, 4},
           ldr.data());
+      // what the viewer displays (ypathtrace.cpp:170, :186): tonemap(hdr, exposure, filmic)
+      // (yocto_color.h:306-316) and the 8-bit conversion, for two settings
+      auto tm = [&](const char* name, float exposure, bool filmic) {
+        auto bytes = std::vector<vec4b>(image.pixels.size());
+        for (size_t i = 0; i < bytes.size(); i++)
+          bytes[i] = float_to_byte(tonemap(image.pixels[i], exposure, filmic, true));
+        out.add(name, vpt::dt_u8, {(uint64_t)state.height, (uint64_t)state.width, 4}, bytes.data());
+      };
+      tm("image_tonemapped8_filmic_e1.5", 1.5f, true);
+      tm("image_tonemapped8_e-0.75", -0.75f, false);
     }
     int meta[4] = {state.width, state.height, state.samples,
         (int)std::thread::hardware_concurrency()};

@@ -10,11 +10,12 @@
 //
 // usage: hostsim <scene.vptscene> <out.vptarch> [--shader NAME] [--samples N]
 //        [--resolution R] [--bounces B] [--noimplicitmis] [--stmaxiter M]
-//        [--rays rays.vptarch] [--instance K] [--threads T] [--cull-check]
+//        [--rays rays.vptarch] [--instance K] [--threads T] [--cull-check] [--sdf-cull-check]
 #define VPT_HOST_POOL 1
 #define VPT_STACK_CHECK 1
 #define VPT_WORK_COUNTERS 1
 #define VPT_CULL_CHECK 1
+#define VPT_SDF_CULL_CHECK 1
 #include <chrono>
 #include <cmath>
 #include <cstring>
@@ -144,6 +145,8 @@ int main(int argc, const char** argv) {
     else if (a == "--instance") instance = std::stoi(next());
     else if (a == "--threads") nthreads = std::stoi(next());
     else if (a == "--cull-check") vpt_cull_check_on = true;
+    else if (a == "--sdf-cull-check") vpt_sdf_cull_check_on = true;
+    else if (a == "--sdf-cull") vpt_sdf_cull_mode = std::stoi(next());
   }
   auto error = std::string{};
   auto scene = scene_data{};
@@ -250,6 +253,12 @@ int main(int argc, const char** argv) {
              "wide_visits=%.2f wide_slot_tests=%.2f stale_node_pops=%.2f\n",
           g_work.rounds / paths, g_work.pops / paths, g_work.leaf_pops / paths, g_work.stale_pops / paths,
           g_work.wide_visits / paths, g_work.wide_slot_tests / paths, g_work.stale_node_pops / paths);
+      if (g_work.sdf_scene_evals > 0)
+        printf("hostsim sdf culling: %.2f fields skipped per scene evaluation (%lld evaluations)\n",
+            (double)g_work.sdf_skips / (double)g_work.sdf_scene_evals, (long long)g_work.sdf_scene_evals);
+      if (vpt_sdf_cull_check_on)
+        printf("hostsim: sdf cull check: %lld fields skipped, %lld of them at or below the running "
+               "minimum\n", (long long)g_work.sdf_skips, (long long)g_work.sdf_skips_wrong);
       if (vpt_cull_check_on)
         printf("hostsim: cull check: %lld instances culled, %lld of them hold a hit the reference "
                "would find\n", (long long)g_work.culled, (long long)g_work.cull_wrong);

@@ -134,6 +134,26 @@ def test_instance_culling_never_hides_a_hit(vpt, hostsim, tmp_path):
     assert np.array_equal(got["rngs_after"], ref["rngs_after"])
 
 
+@pytest.mark.parametrize("mode", [1, 2])
+def test_sdf_field_culling_is_exact(vpt, hostsim, tmp_path, mode):
+    """sdf.cuh eval_sdf_scene_culled (a distance field whose conservative lower bound is above
+    the running minimum is not evaluated; opt-in, the shipped kernels scan all fields): every
+    skipped field is evaluated anyway and must lie strictly above the running minimum, and the
+    image equals the reference's golden bit for bit."""
+    import re
+    scene, shader, spp, res, bounces = "sdf_small", "implicit", 2, 64, 4
+    out = str(tmp_path / "h.vptarch")
+    r = subprocess.run([hostsim, util.scene_path(scene), out, "--shader", shader, "--samples", str(spp),
+                        "--resolution", str(res), "--bounces", str(bounces), "--sdf-cull", str(mode),
+                        "--sdf-cull-check"], check=True, capture_output=True, text=True)
+    m = re.search(r"sdf cull check: (\d+) fields skipped, (\d+) of them", r.stdout)
+    assert m, r.stdout
+    assert int(m.group(1)) > 1000 and int(m.group(2)) == 0, r.stdout
+    got, ref = vpt.archive.load(out), golden(vpt, scene, shader, spp, res, bounces)
+    assert not util.bit_mismatch(got["image_sum"], ref["image_sum"]).any()
+    assert np.array_equal(got["rngs_after"], ref["rngs_after"])
+
+
 # ---- host structures -----------------------------------------------------------------------------
 def test_host_bvh_is_the_reference_bvh(vpt):
     """make_bvh (host/vpt_bvh.cpp) vs yocto's make_bvh: nodes byte for byte, primitive order equal."""

@@ -8,7 +8,10 @@
 // loaders, see tools/vpt_export.cpp); --interactive is unavailable on
 // this box (no OpenGL); the image writers are .hdr / .pfm / .ppm / .png.
 // Added flags: --pipeline {auto,mega,wavefront}, --batch N, --device K, --device-lights
-// (make_lights on the GPU).
+// (make_lights on the GPU), --gpus N (sample ranges over N GPUs of the box, summed on the first),
+// --exposure / --filmic / --pratio (pathtrace_params fields the reference CLI leaves at their
+// defaults) with --display IMG / --display-every N: the viewer's display loop
+// (ypathtrace.cpp:156-189) without a window.
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -148,13 +151,17 @@ int main(int argc, const char** argv) {
   auto interactive = false;
   auto device      = 0;
   auto device_lights = false;
+  auto display       = std::string{};  // headless stand-in for the viewer's display loop
+  auto display_every = 0;
   auto params      = pathtrace_params{};
   params.batch     = 16;
   auto usage       = [&]() {
     printf("usage: ypathtrace [--scene S.vptscene] [--output IMG] [--interactive]\n"
            "  [--resolution 1..4096] [--shader NAME] [--samples 1..4096] [--bounces 1..128]\n"
            "  [--noparallel] [--noimplicitmis] [--stmaxiter 1..512]\n"
-           "  [--pipeline auto|mega|wavefront] [--batch N] [--device K] [--device-lights]\n  shaders:");
+           "  [--pipeline auto|mega|wavefront] [--batch N] [--device K] [--device-lights]\n"
+           "  [--gpus N] [--exposure E] [--filmic] [--pratio P] [--display IMG.ppm|png]\n"
+           "  [--display-every N]\n  shaders:");
     for (auto& n : pathtrace_shader_names) printf(" %s", n.c_str());
     printf("\n");
   };
@@ -181,6 +188,12 @@ int main(int argc, const char** argv) {
     else if (a == "--batch") params.batch = ranged("batch", next(), 1, 4096);
     else if (a == "--device") device = std::stoi(next());
     else if (a == "--device-lights") device_lights = true;
+    else if (a == "--gpus") params.gpus = ranged("gpus", next(), 1, 64);
+    else if (a == "--exposure") params.exposure = std::stof(next());
+    else if (a == "--filmic") params.filmic = true;
+    else if (a == "--pratio") params.pratio = ranged("pratio", next(), 1, 64);
+    else if (a == "--display") display = next();
+    else if (a == "--display-every") display_every = ranged("display-every", next(), 1, 4096);
     else if (a == "--shader") {
       auto name = next(), found = std::string{};
       for (size_t k = 0; k < pathtrace_shader_names.size(); k++)
@@ -217,10 +230,11 @@ int main(int argc, const char** argv) {
     t0          = clock();
     auto lights = pathtrace_lights{};
     auto state  = pathtrace_state{};
+    auto dscene = std::shared_ptr<device_scene>{};
     if (device_lights) {
       // make_lights on the device: the host object stays empty and only keys the cache
       auto stats  = vpt_lights_stats{};
-      auto dscene = upload_scene_device_lights(scene, bvh, &stats);
+      dscene      = upload_scene_device_lights(scene, bvh, &stats);
       printf("build lights (device): %.3f s (%d lights, %llu cdf entries: weights %.2f ms, "
              "running sums %.2f ms)\n", since(t0), stats.num_lights,
           (unsigned long long)stats.cdf_elements, stats.weights_ms, stats.scan_ms);
@@ -229,19 +243,58 @@ int main(int argc, const char** argv) {
     } else {
       lights = make_lights(scene, params);
       printf("build lights: %.3f s\n", since(t0));
+      t0     = clock();
+      dscene = upload_scene(scene, bvh, lights);
+      printf("upload scene: %.3f s\n", since(t0));
       state = make_state(scene, params);
+      bind_device_scene(state, dscene, scene, bvh, lights);
+    }
+    // The viewer's display loop without a window (apps/ypathtrace/ypathtrace.cpp:156-189): a
+    // one-sample preview at resolution / pratio blown up to the frame, then the tonemapped
+    // frame every `display_every` samples - tonemap + 8-bit conversion run on the device, the
+    // bytes arrive through the state's pinned buffer and go to the --display file
+    auto show = [&](const std::vector<uint8_t>& rgba, int w, int h) {
+      auto none = color_image{};
+      none.width = w, none.height = h;
+      if (!save_image(display, none, error, rgba)) print_fatal(error);
+    };
+    if (!display.empty()) {
+      auto pparams = params;
+      pparams.resolution = std::max(1, params.resolution / params.pratio);
+      pparams.samples = 1, pparams.batch = 1, pparams.gpus = 1;
+      auto pstate = make_state(scene, pparams);
+      bind_device_scene(pstate, dscene, scene, bvh, lights);
+      pathtrace_samples(pstate, scene, bvh, lights, pparams);
+      auto small = get_render_tonemapped8(pstate, params.exposure, params.filmic);
+      auto frame = std::vector<uint8_t>((size_t)state.width * state.height * 4);
+      for (auto idx = 0; idx < state.width * state.height; idx++) {
+        auto i  = idx % state.width, j = idx / state.width;
+        auto pi = std::min(i / params.pratio, pstate.width - 1),
+             pj = std::min(j / params.pratio, pstate.height - 1);
+        memcpy(&frame[(size_t)idx * 4], &small[((size_t)pj * pstate.width + pi) * 4], 4);
+      }
+      show(frame, state.width, state.height);
+      printf("preview: %dx%d, 1 sample -> %s\n", pstate.width, pstate.height, display.c_str());
     }
     t0         = clock();
+    int shown  = 0;
     while (state.samples < params.samples) {
       pathtrace_samples(state, scene, bvh, lights, params);
       printf("\rrender samples: %d/%d", state.samples, params.samples);
       fflush(stdout);
+      if (!display.empty() && display_every > 0 && state.samples - shown >= display_every) {
+        show(get_render_tonemapped8(state, params.exposure, params.filmic), state.width, state.height);
+        shown = state.samples;
+      }
     }
+    if (!display.empty())
+      show(get_render_tonemapped8(state, params.exposure, params.filmic), state.width, state.height);
     auto render  = get_render(state);
     auto seconds = since(t0);
-    printf("\nrender: %.3f s, %.2f Mpaths/s (%dx%d, %d spp, %s)\n", seconds,
+    printf("\nrender: %.3f s, %.2f Mpaths/s (%dx%d, %d spp, %s, %d GPU%s)\n", seconds,
         (double)state.width * state.height * state.samples / seconds / 1e6, state.width,
-        state.height, state.samples, pathtrace_shader_names[(int)params.shader].c_str());
+        state.height, state.samples, pathtrace_shader_names[(int)params.shader].c_str(),
+        params.gpus, params.gpus > 1 ? "s" : "");
     auto ldr = outname.size() > 4 && (outname.substr(outname.size() - 4) == ".png" ||
                                          outname.substr(outname.size() - 4) == ".ppm");
     if (!save_image(outname, render, error, ldr ? get_render_srgb8(state) : std::vector<uint8_t>{}))

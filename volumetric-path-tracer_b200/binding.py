@@ -208,11 +208,13 @@ class Scene:
 class Render:
     """make_state + pathtrace_samples + get_render for one scene / params pair."""
 
-    def __init__(self, scene: Scene, params: Params):
+    def __init__(self, scene: Scene, params: Params, gpus: int = 1):
         self._host = libs()[1]
         self.scene, self.params = scene, params
         self._h = C.c_void_p()
         _check(self._host.vpth_render_create(scene._h, C.byref(params), C.byref(self._h)))
+        if gpus > 1:  # sample-range sharding over GPUs of this box, summed inside image()
+            _check(self._host.vpth_render_set_gpus(self._h, gpus))
         w, h = C.c_int32(), C.c_int32()
         _check(self._host.vpth_render_size(self._h, C.byref(w), C.byref(h)))
         self.width, self.height = w.value, h.value
@@ -252,6 +254,13 @@ class Render:
         """Output stage on the device: get_render + rgb_to_srgb + float_to_byte -> [h, w, 4] uint8."""
         out = np.zeros((self.height, self.width, 4), dtype=np.uint8)
         _check(self._host.vpth_render_get_srgb8(self._h, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def image_tonemapped8(self, exposure: float = 0.0, filmic: bool = False) -> np.ndarray:
+        """The viewer's display conversion on the device: tonemap(exposure, filmic) + 8 bit."""
+        out = np.zeros((self.height, self.width, 4), dtype=np.uint8)
+        _check(self._host.vpth_render_get_tonemapped8(self._h, C.c_float(exposure), int(filmic),
+                                                      out.ctypes.data_as(C.POINTER(C.c_uint8))))
         return out
 
     def stats(self) -> TraceStats:

@@ -77,10 +77,16 @@ struct DScene {
   const float* cdf;
   int          num_lights;
   // sdf grids / functions
-  const f4*    vol_instances;  // 4 x f4: frame cols; w = {scalef, volume, material, 0}
+  // 6 x f4: frame cols; w = {scalef, volume, material, 0}; then the proxy box of eval_sdf
+  // (yocto_sdfs.cpp:36-40), constant per instance: {size / 2, 0} {size, 0}
+  const f4*    vol_instances;
   const f4*    volumes;        // 2 x f4: {w, h, d (ints), res} {offset (int), 0, 0, 0}
   const float* voxels;
   const f4*    sdfs;  // 10 x f4: frame(4; w = type, material), inverse rigid (4), params, whd
+  // 2 x f4 per distance field (grid instances, then functions): a world-space box holding the
+  // pre-image of the field's local bounding box {min.xyz, s^2} {max.xyz, 1 if grid}; s bounds
+  // the frame's smallest singular value from below (0: never skip this field), see sdf.cuh
+  const f4*    sdf_bounds;
   int          num_vol_instances;
   int          num_sdfs;
 };

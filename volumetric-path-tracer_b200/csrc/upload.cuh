@@ -13,6 +13,7 @@ inline const char* cudaGetErrorString(cudaError_t) { return "host pool error"; }
 #include <cuda_runtime.h>
 #endif
 
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -21,6 +22,7 @@ inline const char* cudaGetErrorString(cudaError_t) { return "host pool error"; }
 #include "../../include/vpt_cuda.h"
 #include "bvh.cuh"
 #include "dscene.cuh"
+#include "sdf.cuh"
 
 namespace vpt {
 
@@ -111,7 +113,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     return fail(VPT_ERR_INVALID, "shape_bvhs is null");
 
   std::vector<f4>  nodes, wnodes, prims, inst_trav, inst_frame, vcol, materials, cameras, environments;
-  std::vector<f4>  vol_instances, volumes, sdfs, texf;
+  std::vector<f4>  vol_instances, volumes, sdfs, sdf_bounds, texf;
   std::vector<f4>  scene_leaves, inst_root;
   std::vector<i4>  shapes, elems, textures, lights;
   std::vector<float>         vpos, vnrm, vtex, cdf, voxels, srgb_lut(256);
@@ -540,6 +542,73 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   }
 
   // ---- sdf grids and functions -------------------------------------------------------
+  // Culling record of one distance field (dscene.cuh `sdf_bounds`, sdf.cuh): world -> local is
+  // q = M p + o (the FORWARD frame, yocto_sdfs.cpp:13, :20); the field is an exact distance to
+  // a shape inside the local box [lo, hi]. W = bounding box of M^-1 ([lo, hi] - o), enlarged;
+  // s = smallest singular value of M (Jacobi on M^T M, double), shrunk. VPT_NO_SDF_CULL=1: s = 0.
+  const char* no_sdf_cull_env = getenv("VPT_NO_SDF_CULL");
+  const bool  sdf_cull_on     = !(no_sdf_cull_env && atoi(no_sdf_cull_env) != 0);
+  auto push_sdf_bounds = [&](const float* fr, const double lo[3], const double hi[3], bool ok,
+                             bool grid) {
+    f4 b0{0, 0, 0, 0}, b1{0, 0, 0, grid ? 1.0f : 0.0f};
+    auto never = [&]() { sdf_bounds.push_back(b0), sdf_bounds.push_back(b1); };
+    if (!ok || !sdf_cull_on) return never();
+    double m[3][3];  // m[r][c]: column c of the frame is fr[3c .. 3c+2]
+    for (int c = 0; c < 3; c++)
+      for (int r = 0; r < 3; r++) m[r][c] = fr[3 * c + r];
+    double det = m[0][0] * (m[1][1] * m[2][2] - m[1][2] * m[2][1]) -
+                 m[0][1] * (m[1][0] * m[2][2] - m[1][2] * m[2][0]) +
+                 m[0][2] * (m[1][0] * m[2][1] - m[1][1] * m[2][0]);
+    if (!(std::fabs(det) > 1e-30) || !(std::fabs(det) < 1e30)) return never();
+    double inv[3][3];
+    for (int r = 0; r < 3; r++)
+      for (int c = 0; c < 3; c++) {
+        int r1 = (c + 1) % 3, r2 = (c + 2) % 3, c1 = (r + 1) % 3, c2 = (r + 2) % 3;
+        inv[r][c] = (m[r1][c1] * m[r2][c2] - m[r1][c2] * m[r2][c1]) / det;  // adjugate / det
+      }
+    // eigenvalues of A = M^T M by cyclic Jacobi rotations
+    double a[3][3];
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) a[i][j] = m[0][i] * m[0][j] + m[1][i] * m[1][j] + m[2][i] * m[2][j];
+    for (int sweep = 0; sweep < 32; sweep++)
+      for (int pi = 0; pi < 2; pi++)
+        for (int qi = pi + 1; qi < 3; qi++) {
+          if (std::fabs(a[pi][qi]) < 1e-300) continue;
+          double th = (a[qi][qi] - a[pi][pi]) / (2 * a[pi][qi]);
+          double tt = (th >= 0 ? 1 : -1) / (std::fabs(th) + std::sqrt(th * th + 1));
+          double cs = 1 / std::sqrt(tt * tt + 1), sn = tt * cs;
+          for (int k = 0; k < 3; k++) {
+            double akp = a[k][pi], akq = a[k][qi];
+            a[k][pi] = cs * akp - sn * akq, a[k][qi] = sn * akp + cs * akq;
+          }
+          for (int k = 0; k < 3; k++) {
+            double apk = a[pi][k], aqk = a[qi][k];
+            a[pi][k] = cs * apk - sn * aqk, a[qi][k] = sn * apk + cs * aqk;
+          }
+        }
+    double lmin = std::fmin(a[0][0], std::fmin(a[1][1], a[2][2]));
+    if (!(lmin > 0)) return never();
+    double smin = std::sqrt(lmin) * (1 - 1e-3);
+    double wmin[3] = {1e300, 1e300, 1e300}, wmax[3] = {-1e300, -1e300, -1e300};
+    for (int c = 0; c < 8; c++) {
+      double q[3] = {(c & 1 ? hi[0] : lo[0]) - fr[9], (c & 2 ? hi[1] : lo[1]) - fr[10],
+          (c & 4 ? hi[2] : lo[2]) - fr[11]};
+      for (int k = 0; k < 3; k++) {
+        double w = inv[k][0] * q[0] + inv[k][1] * q[1] + inv[k][2] * q[2];
+        if (!(w >= -1e30 && w <= 1e30)) return never();
+        wmin[k] = std::fmin(wmin[k], w), wmax[k] = std::fmax(wmax[k], w);
+      }
+    }
+    double scale = 0;
+    for (int k = 0; k < 3; k++)
+      scale = std::fmax(scale, (wmax[k] - wmin[k]) + std::fmax(std::fabs(wmin[k]), std::fabs(wmax[k])));
+    double margin = 1e-4 * scale + 1e-30;
+    b0 = {(float)(wmin[0] - margin), (float)(wmin[1] - margin), (float)(wmin[2] - margin),
+        (float)(smin * smin)};
+    b1 = {(float)(wmax[0] + margin), (float)(wmax[1] + margin), (float)(wmax[2] + margin),
+        grid ? 1.0f : 0.0f};
+    sdf_bounds.push_back(b0), sdf_bounds.push_back(b1);
+  };
   for (int v = 0; v < in.num_volumes; v++) {
     auto&  vol = in.volumes[v];
     if (vol.whd[0] <= 0 || vol.whd[1] <= 0 || vol.whd[2] <= 0 || !vol.voxels)
@@ -559,6 +628,20 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     vol_instances.push_back(pack(frame.y, vi.volume));
     vol_instances.push_back(pack(frame.z, vi.material));
     vol_instances.push_back(pack(frame.o, 0));
+    auto& gv   = in.volumes[vi.volume];
+    auto  size = proxy_box_size(frame.o, gv.whd[0], gv.whd[1], gv.whd[2], gv.res, vi.scalef);
+    vol_instances.push_back(pack(size * 0.5f, 0));
+    vol_instances.push_back(pack(size, 0));
+    // the proxy box of eval_sdf (yocto_sdfs.cpp:36-40): [o, o + res whd scalef] in LOCAL space
+    auto&  vol = in.volumes[vi.volume];
+    double lo[3], hi[3];
+    bool   ok = true;
+    for (int k = 0; k < 3; k++) {
+      double size = (double)vol.res * vol.whd[k] * vi.scalef;
+      lo[k] = 0, hi[k] = size * (1 + 1e-5);
+      ok    = ok && size > 0 && size < 1e30;
+    }
+    push_sdf_bounds(vi.frame, lo, hi, ok, true);
   }
   for (int s = 0; s < in.num_sdfs; s++) {
     auto& sd = in.sdfs[s];
@@ -572,6 +655,33 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     sdfs.push_back(pack(inv.z, 0)), sdfs.push_back(pack(inv.o, 0));
     sdfs.push_back({sd.params[0], sd.params[1], sd.params[2], sd.params[3]});
     sdfs.push_back({sd.whd[0], sd.whd[1], sd.whd[2], 0});
+    // local bounding box of the shape each typed closure measures the distance to
+    // (yocto_sceneio.cpp:3690-3726, yocto_sdfs.h:43-80); a plane has none
+    double lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    bool   ok = true;
+    auto   sym = [&](double x, double y, double z) {
+      ok = ok && x >= 0 && y >= 0 && z >= 0;
+      lo[0] = -x, lo[1] = -y, lo[2] = -z, hi[0] = x, hi[1] = y, hi[2] = z;
+    };
+    switch (sd.type) {
+      case VPT_SDF_BBOX: sym(sd.params[1], sd.params[2], sd.params[3]); ok = ok && sd.params[0] >= 0; break;
+      case VPT_SDF_BOX:
+        for (int k = 0; k < 3; k++) hi[k] = sd.whd[k], ok = ok && sd.whd[k] >= 0;
+        break;
+      case VPT_SDF_CAPPED_CONE: {
+        double r = std::fmax(sd.params[1], sd.params[2]);
+        sym(r, sd.params[0], r);
+        ok = ok && sd.params[1] >= 0 && sd.params[2] >= 0;
+      } break;
+      case VPT_SDF_SPHERE: sym(sd.params[0], sd.params[0], sd.params[0]); break;
+      case VPT_SDF_TORUS:
+        sym((double)sd.params[0] + sd.params[1], sd.params[1], (double)sd.params[0] + sd.params[1]);
+        ok = ok && sd.params[0] >= 0;
+        break;
+      default: ok = false; break;  // plane: unbounded
+    }
+    for (int k = 0; k < 3; k++) ok = ok && std::isfinite(lo[k]) && std::isfinite(hi[k]);
+    push_sdf_bounds(sd.frame, lo, hi, ok, false);
   }
 
   // offsets into the pools are stored as int
@@ -613,6 +723,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
   VPT_UP(volumes, volumes);
   VPT_UP(voxels, voxels);
   VPT_UP(sdfs, sdfs);
+  VPT_UP(sdf_bounds, sdf_bounds);
 #undef VPT_UP
   if (e != cudaSuccess) {
     p.release();

@@ -64,7 +64,8 @@ struct work_counters {
       instance_queries{0}, sdf_scene_evals{0}, sdf_fn_evals{0}, sdf_grid_evals{0},
       trilinear{0}, bounces{0}, lightpdf_calls{0}, texel_reads{0}, iq_box_tests{0}, iq_tri_tests{0},
       cull_tests{0}, culled{0}, cull_wrong{0}, node_visits{0}, pops{0}, stale_pops{0}, leaf_pops{0},
-      rounds{0}, wide_visits{0}, wide_slot_tests{0}, stale_node_pops{0};
+      rounds{0}, wide_visits{0}, wide_slot_tests{0}, stale_node_pops{0}, sdf_skips{0},
+      sdf_skips_wrong{0};
 };
 inline work_counters g_work;
 }  // namespace vpt

@@ -7,10 +7,13 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/vpt_cuda.h"
 #include "shaders.cuh"
@@ -66,6 +69,12 @@ struct vpt_state {
   wavefront_buffers wf;
   cudaEvent_t     ev0 = nullptr, ev1 = nullptr;
   vpt_trace_stats stats{};
+  // multi-GPU accumulation: states whose images are summed into this one's downloads
+  std::vector<vpt_state*> peers;
+  f4*             reduced = nullptr;  // root image + peers' images (root's device)
+  f4*             staging = nullptr;  // a peer image copied over when P2P loads are unavailable
+  uchar4*         out8    = nullptr;  // device side of download_srgb8
+  uint8_t*        pinned8 = nullptr;  // pinned host side of download_srgb8
 };
 
 // ---------------------------------------------------------------------------
@@ -202,13 +211,23 @@ __device__ __forceinline__ float out_rgb_to_srgb(float rgb) {
 __device__ __forceinline__ unsigned char out_float_to_byte(float a) {
   return (unsigned char)vpt::vclamp((int)(a * 256), 0, 255);
 }
+// `gain` = exp2(exposure), evaluated by the host libm as the reference does (std::exp2,
+// yocto_color.h:308), 1 for exposure 0; filmic = the ACES fit of tonemap_filmic
+// (yocto_color.h:274-281), expression for expression, no FMA contraction
 __global__ void k_output_srgb8(const vpt::f4* __restrict__ image, uchar4* __restrict__ out,
-    size_t pixels, float scale) {
+    size_t pixels, float scale, float gain, int apply_gain, int filmic) {
   size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= pixels) return;
-  auto p = image[idx] * scale;
-  out[idx] = make_uchar4(out_float_to_byte(out_rgb_to_srgb(p.x)),
-      out_float_to_byte(out_rgb_to_srgb(p.y)), out_float_to_byte(out_rgb_to_srgb(p.z)),
+  auto p   = image[idx] * scale;
+  auto rgb = vpt::f3{p.x, p.y, p.z};
+  if (apply_gain) rgb = rgb * gain;
+  if (filmic) {
+    auto hdr = rgb * 0.6f;
+    auto ldr = (hdr * hdr * 2.51f + hdr * 0.03f) / (hdr * hdr * 2.43f + hdr * 0.59f + 0.14f);
+    rgb = {vpt::vmax(0.0f, ldr.x), vpt::vmax(0.0f, ldr.y), vpt::vmax(0.0f, ldr.z)};
+  }
+  out[idx] = make_uchar4(out_float_to_byte(out_rgb_to_srgb(rgb.x)),
+      out_float_to_byte(out_rgb_to_srgb(rgb.y)), out_float_to_byte(out_rgb_to_srgb(rgb.z)),
       out_float_to_byte(p.w));
 }
 
@@ -241,6 +260,16 @@ int vpt_cuda_set_device(int device) {
   if (auto r = require_device()) return r;
   VPT_CUDA_TRY(cudaSetDevice(device));
   return VPT_OK;
+}
+
+int vpt_cuda_current_device(void) {
+  int  device = 0;
+  auto e      = cudaGetDevice(&device);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return -1;
+  }
+  return device;
 }
 
 const char* vpt_cuda_last_error(void) { return g_last_error.c_str(); }
@@ -505,6 +534,10 @@ void vpt_cuda_free_state(vpt_state* state) {
   if (!state) return;
   cudaFree(state->image);
   cudaFree(state->rngs);
+  if (state->reduced) cudaFree(state->reduced);
+  if (state->staging) cudaFree(state->staging);
+  if (state->out8) cudaFree(state->out8);
+  if (state->pinned8) cudaFreeHost(state->pinned8);
   state->wf.release();
   if (state->ev0) cudaEventDestroy(state->ev0);
   if (state->ev1) cudaEventDestroy(state->ev1);
@@ -577,28 +610,122 @@ int vpt_cuda_get_trace_stats(const vpt_state* state, vpt_trace_stats* stats) {
   return VPT_OK;
 }
 
+// Sum of the root's and its peers' accumulation images on the root's device (SURVEY 8(b)/(e):
+// "vpt_cuda_download_image performs the reduce if multi-GPU"). One kernel reads every peer's
+// image through P2P loads over NVLink (k_reduce_images); a peer the root cannot map is copied
+// over first. The root's own image is left alone, so downloads stay idempotent. Returns the
+// image to read (state->image when there are no peers).
+static int reduced_image(vpt_state* state, const f4** out) {
+  *out = state->image;
+  if (state->peers.empty()) return VPT_OK;
+  size_t pixels = (size_t)state->width * state->height;
+  int    current = 0;
+  VPT_CUDA_TRY(cudaGetDevice(&current));
+  if (current != state->device) VPT_CUDA_TRY(cudaSetDevice(state->device));
+  if (!state->reduced) VPT_CUDA_TRY(cudaMalloc(&state->reduced, pixels * sizeof(f4)));
+  VPT_CUDA_TRY(cudaMemcpy(state->reduced, state->image, pixels * sizeof(f4), cudaMemcpyDeviceToDevice));
+  peer_list direct{};
+  int       ndirect = 0;
+  auto flush = [&]() -> cudaError_t {
+    if (!ndirect) return cudaSuccess;
+    k_reduce_images<<<(unsigned)((pixels + 255) / 256), 256>>>((float*)state->reduced, direct,
+        ndirect, pixels);
+    ndirect = 0;
+    return cudaGetLastError();
+  };
+  for (auto peer : state->peers) {
+    bool mapped = peer->device == state->device;
+    if (!mapped) {
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, state->device, peer->device);
+      if (can) {
+        auto e = cudaDeviceEnablePeerAccess(peer->device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError(), e = cudaSuccess;
+        mapped = e == cudaSuccess;
+        if (!mapped) cudaGetLastError();
+      }
+    }
+    if (mapped) {
+      direct.p[ndirect++] = (const float*)peer->image;
+      if (ndirect == 16) VPT_CUDA_TRY(flush());
+    } else {
+      VPT_CUDA_TRY(flush());
+      if (!state->staging) VPT_CUDA_TRY(cudaMalloc(&state->staging, pixels * sizeof(f4)));
+      VPT_CUDA_TRY(cudaMemcpyPeer(state->staging, state->device, peer->image, peer->device,
+          pixels * sizeof(f4)));
+      direct.p[ndirect++] = (const float*)state->staging;
+      VPT_CUDA_TRY(flush());
+    }
+  }
+  VPT_CUDA_TRY(flush());
+  VPT_CUDA_TRY(cudaDeviceSynchronize());
+  if (current != state->device) VPT_CUDA_TRY(cudaSetDevice(current));
+  *out = state->reduced;
+  return VPT_OK;
+}
+
+int vpt_cuda_state_add_peer(vpt_state* root, vpt_state* peer) {
+  if (!root || !peer || root == peer) return set_error(VPT_ERR_INVALID, "bad argument");
+  if (root->width != peer->width || root->height != peer->height)
+    return set_error(VPT_ERR_INVALID, "image should have the same size");
+  if (!peer->peers.empty()) return set_error(VPT_ERR_INVALID, "a peer cannot have peers of its own");
+  for (auto p : root->peers)
+    if (p == peer) return VPT_OK;
+  root->peers.push_back(peer);
+  return VPT_OK;
+}
+
+int vpt_cuda_state_remove_peers(vpt_state* root) {
+  if (!root) return set_error(VPT_ERR_INVALID, "null state");
+  root->peers.clear();
+  return VPT_OK;
+}
+
+int vpt_cuda_state_total_samples(const vpt_state* state) {
+  if (!state) return 0;
+  int total = state->samples;
+  for (auto p : state->peers) total += p->samples;
+  return total;
+}
+
 int vpt_cuda_download_image(vpt_state* state, float* rgba, size_t n) {
   if (!state || !rgba) return set_error(VPT_ERR_INVALID, "null argument");
   size_t want = (size_t)state->width * state->height * 4;
   if (n != want) return set_error(VPT_ERR_INVALID, "image should have the same size");
-  VPT_CUDA_TRY(cudaMemcpy(rgba, state->image, want * sizeof(float), cudaMemcpyDeviceToHost));
+  const f4* image = nullptr;
+  if (auto r = reduced_image(state, &image)) return r;
+  VPT_CUDA_TRY(cudaMemcpy(rgba, image, want * sizeof(float), cudaMemcpyDeviceToHost));
   return VPT_OK;
 }
 
+// exposure + filmic tonemap of the reference's display path (tonemap, yocto_color.h / the
+// viewer's params.exposure / params.filmic, ypathtrace.cpp:159-189): rgb * 2^exposure, optional
+// ACES-fitted filmic curve, then rgb_to_srgb + float_to_byte as save_image does
+int vpt_cuda_download_tonemapped8(vpt_state* state, int samples, float exposure, int filmic,
+    uint8_t* rgba, size_t n);
+
 int vpt_cuda_download_srgb8(vpt_state* state, int samples, uint8_t* rgba, size_t n) {
+  return vpt_cuda_download_tonemapped8(state, samples, 0.0f, 0, rgba, n);
+}
+
+int vpt_cuda_download_tonemapped8(vpt_state* state, int samples, float exposure, int filmic,
+    uint8_t* rgba, size_t n) {
   if (auto r = require_device()) return r;
   if (!state || !rgba) return set_error(VPT_ERR_INVALID, "null argument");
   size_t pixels = (size_t)state->width * state->height;
   if (n != pixels * 4) return set_error(VPT_ERR_INVALID, "image should have the same size");
-  if (samples <= 0) samples = state->samples;
+  if (samples <= 0) samples = vpt_cuda_state_total_samples(state);
   if (samples <= 0) return set_error(VPT_ERR_INVALID, "nothing rendered yet");
-  uchar4* dev = nullptr;
-  VPT_CUDA_TRY(cudaMalloc(&dev, pixels * sizeof(uchar4)));
-  k_output_srgb8<<<(unsigned)((pixels + 255) / 256), 256>>>(state->image, dev, pixels,
-      1.0f / (float)samples);
-  auto e = cudaMemcpy(rgba, dev, pixels * sizeof(uchar4), cudaMemcpyDeviceToHost);
-  cudaFree(dev);
-  if (e != cudaSuccess) return cuda_fail(e, "download_srgb8");
+  const f4* image = nullptr;
+  if (auto r = reduced_image(state, &image)) return r;
+  // device and pinned host buffers are kept with the state: a preview loop calls this per frame
+  if (!state->out8) VPT_CUDA_TRY(cudaMalloc(&state->out8, pixels * sizeof(uchar4)));
+  if (!state->pinned8) VPT_CUDA_TRY(cudaMallocHost(&state->pinned8, pixels * sizeof(uchar4)));
+  k_output_srgb8<<<(unsigned)((pixels + 255) / 256), 256>>>(image, state->out8, pixels,
+      1.0f / (float)samples, exp2f(exposure), exposure != 0 ? 1 : 0, filmic ? 1 : 0);
+  VPT_CUDA_TRY(cudaGetLastError());
+  VPT_CUDA_TRY(cudaMemcpy(state->pinned8, state->out8, pixels * sizeof(uchar4), cudaMemcpyDeviceToHost));
+  memcpy(rgba, state->pinned8, pixels * sizeof(uchar4));
   return VPT_OK;
 }
 

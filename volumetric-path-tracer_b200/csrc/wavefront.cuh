@@ -467,7 +467,7 @@ __global__ void __launch_bounds__(wf_block)
   if (isec.hit) {
     int material;
     if (is_sdf_shader<S>())
-      material = isec.instance != invalidid ? f2i(ld4(sc.vol_instances + 4 * isec.instance + 2).w)
+      material = isec.instance != invalidid ? f2i(ld4(sc.vol_instances + vol_inst_f4 * isec.instance + 2).w)
                                             : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
     else
       material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);
@@ -607,7 +607,7 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
         int material;
         if constexpr (sdf)
           material = isec.instance != invalidid
-                         ? f2i(ld4(sc.vol_instances + 4 * isec.instance + 2).w)
+                         ? f2i(ld4(sc.vol_instances + vol_inst_f4 * isec.instance + 2).w)
                          : f2i(ld4(sc.sdfs + 10 * isec.element + 1).w);
         else
           material = f2i(ld4(sc.inst_trav + 4 * isec.instance + 3).w);

@@ -211,31 +211,7 @@ int vpth_render_get_rngs(vpth_render* r, uint64_t* rngs) {
 
 int vpth_render_reset(vpth_render* r, uint64_t rng_offset) {
   if (!r) return VPT_ERR_INVALID;
-  return guarded([&] {
-    r->state.samples = 0;
-    if (auto dstate = device_handle(r->state)) {
-      // straight from the pinned initial generators; the host mirrors are refreshed lazily
-      if (vpt_cuda_reset_state(dstate, (const uint64_t*)r->initial_rngs.data()) != VPT_OK)
-        throw std::runtime_error(vpt_cuda_last_error());
-      if (rng_offset && vpt_cuda_advance_rngs(dstate, rng_offset) != VPT_OK)
-        throw std::runtime_error(vpt_cuda_last_error());
-      mark_host_stale(r->state);
-      return;
-    }
-    r->state.rngs = r->initial_rngs;
-    r->state.image.assign(r->state.image.size(), {0, 0, 0, 0});
-    if (rng_offset) {
-      // no device state yet: jump the host copies (same O(log n) recurrence)
-      for (auto& g : r->state.rngs) {
-        uint64_t cur_mult = 6364136223846793005ULL, cur_plus = g.inc, acc_mult = 1, acc_plus = 0;
-        for (auto delta = rng_offset; delta > 0; delta >>= 1) {
-          if (delta & 1) acc_mult *= cur_mult, acc_plus = acc_plus * cur_mult + cur_plus;
-          cur_plus = (cur_mult + 1) * cur_plus, cur_mult *= cur_mult;
-        }
-        g.state = acc_mult * g.state + acc_plus;
-      }
-    }
-  });
+  return guarded([&] { reset_device_state(r->state, r->initial_rngs, rng_offset); });
 }
 
 int vpth_render_samples(vpth_render* r, int nsamples) {
@@ -249,6 +225,12 @@ int vpth_render_samples(vpth_render* r, int nsamples) {
     params.batch = nsamples;
     pathtrace_samples(r->state, s->scene, s->bvh, s->lights, params);
   });
+}
+
+int vpth_render_set_gpus(vpth_render* r, int gpus) {
+  if (!r || gpus < 1) return VPT_ERR_INVALID;
+  r->params.gpus = gpus;
+  return VPT_OK;
 }
 
 int vpth_render_done_samples(const vpth_render* r) { return r ? r->state.samples : 0; }
@@ -271,6 +253,14 @@ int vpth_render_get_srgb8(vpth_render* r, uint8_t* rgba) {
   if (!r || !rgba) return VPT_ERR_INVALID;
   return guarded([&] {
     auto bytes = get_render_srgb8(r->state);
+    memcpy(rgba, bytes.data(), bytes.size());
+  });
+}
+
+int vpth_render_get_tonemapped8(vpth_render* r, float exposure, int filmic, uint8_t* rgba) {
+  if (!r || !rgba) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto bytes = get_render_tonemapped8(r->state, exposure, filmic != 0);
     memcpy(rgba, bytes.data(), bytes.size());
   });
 }

@@ -4,6 +4,10 @@
 // layer (include/vpt_cuda.h). No rendering happens on the host.
 #include "vpt_pathtrace.h"
 
+#include <algorithm>
+#include <cstdlib>
+#include <thread>
+
 #include <cmath>
 #include <cstring>
 
@@ -138,8 +142,31 @@ struct device_scene {
   }
 };
 
+// scene replica + accumulation state of one more GPU (multi-GPU rendering, params.gpus > 1)
+struct device_replica {
+  int        device = 0;
+  vpt_scene* scene  = nullptr;
+  vpt_state* state  = nullptr;
+  ~device_replica() {
+    // free on the device that owns them
+    int current = 0;
+    if (scene || state) {
+      current = vpt_cuda_current_device();
+      vpt_cuda_set_device(device);
+    }
+    if (state) vpt_cuda_free_state(state);
+    if (scene) vpt_cuda_free_scene(scene);
+    if (scene || state) vpt_cuda_set_device(current);
+  }
+};
+
 struct device_binding {
   std::shared_ptr<device_scene> scene = {};
+  std::vector<std::unique_ptr<device_replica>> replicas = {};
+  int         root_device = 0;
+  // what every GPU's generators derive from: base_rngs advanced by rng_offset (+ rank << 40)
+  std::vector<rng_state> base_rngs = {};
+  uint64_t    rng_offset  = 0;
   vpt_state*  state     = nullptr;
   const void* scene_key = nullptr;
   const void* bvh_key   = nullptr;
@@ -147,6 +174,8 @@ struct device_binding {
   bool        dirty     = false;  // device image is ahead of state.image
   bool        dirty_rngs = false; // device generators are ahead of state.rngs
   ~device_binding() {
+    if (state) vpt_cuda_state_remove_peers(state);
+    replicas.clear();
     if (state) vpt_cuda_free_state(state);
   }
 };
@@ -334,8 +363,55 @@ static device_binding& bind(pathtrace_state& state, const scene_data& scene,
     check(vpt_cuda_create_state(state.width, state.height, (const uint64_t*)state.rngs.data(),
               &dev.state),
         "vpt_cuda_create_state");
+    if (dev.base_rngs.empty()) dev.base_rngs = state.rngs, dev.rng_offset = 0;
   }
   return dev;
+}
+
+// GPUs 1 .. gpus-1: upload a replica of the scene, create a state whose generators run
+// rank << 40 draws ahead, and join it to the root state (the reduce happens in the downloads)
+static void bind_replicas(device_binding& dev, pathtrace_state& state, const scene_data& scene,
+    const bvh_scene& bvh, const pathtrace_lights& lights, int gpus) {
+  if ((int)dev.replicas.size() == gpus - 1) return;
+  int visible = vpt_cuda_device_count();
+  // VPT_GPUS_OVERSUBSCRIBE=1 (tests on a one-GPU box): ranks wrap around the visible devices
+  auto wrap_env = getenv("VPT_GPUS_OVERSUBSCRIBE");
+  bool wrap     = wrap_env && atoi(wrap_env) != 0;
+  if (gpus > visible && !wrap)
+    throw std::runtime_error(std::to_string(gpus) + " GPUs requested, " + std::to_string(visible) +
+                             " visible");
+  check(vpt_cuda_state_remove_peers(dev.state), "vpt_cuda_state_remove_peers");
+  dev.replicas.clear();
+  dev.root_device = vpt_cuda_current_device();
+  auto storage = scene_desc_storage{};
+  make_scene_desc(storage, scene, bvh, lights);
+  auto errors  = std::vector<std::string>(gpus);
+  auto workers = std::vector<std::thread>{};
+  for (int r = 1; r < gpus; r++) dev.replicas.push_back(std::make_unique<device_replica>());
+  for (int r = 1; r < gpus; r++) {
+    workers.emplace_back([&, r] {
+      auto& rep  = *dev.replicas[r - 1];
+      rep.device = (dev.root_device + r) % visible;
+      auto ok = [&](int status) {
+        if (status != VPT_OK && errors[r].empty()) errors[r] = vpt_cuda_last_error();
+        return status == VPT_OK;
+      };
+      if (!ok(vpt_cuda_set_device(rep.device))) return;
+      if (!ok(vpt_cuda_upload_scene(&storage.desc, &rep.scene))) return;
+      if (!ok(vpt_cuda_create_state(state.width, state.height,
+              (const uint64_t*)dev.base_rngs.data(), &rep.state)))
+        return;
+      ok(vpt_cuda_advance_rngs(rep.state, dev.rng_offset + rank_rng_offset(r)));
+    });
+  }
+  for (auto& w : workers) w.join();
+  for (auto& e : errors)
+    if (!e.empty()) {
+      dev.replicas.clear();
+      throw std::runtime_error("multi-GPU set-up: " + e);
+    }
+  for (auto& rep : dev.replicas)
+    check(vpt_cuda_state_add_peer(dev.state, rep->state), "vpt_cuda_state_add_peer");
 }
 
 void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
@@ -345,9 +421,41 @@ void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bv
     throw std::runtime_error("sampler unknown");
   auto& dev     = bind(state, scene, bvh, lights);
   auto  cparams = to_c_params(params);
-  check(vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams, params.batch > 0 ? params.batch : 1),
-      "vpt_cuda_trace_samples");
-  state.samples = vpt_cuda_state_samples(dev.state);
+  int   batch   = params.batch > 0 ? params.batch : 1;
+  int   gpus    = params.gpus > 1 ? params.gpus : 1;
+  if (gpus == 1) {
+    check(vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams, batch),
+        "vpt_cuda_trace_samples");
+    state.samples = vpt_cuda_state_samples(dev.state);
+    dev.dirty = dev.dirty_rngs = true;
+    return;
+  }
+  // sample-range sharding: this call's `batch` samples (capped by the total target) are split
+  // over the GPUs; one host thread per GPU drives its wavefront, the caller's thread the root's
+  bind_replicas(dev, state, scene, bvh, lights, gpus);
+  batch = std::min(batch, params.samples - state.samples);
+  // a rank's own target is open-ended (the split decides how much it runs); samples == 1 keeps
+  // selecting the preview branch (yocto_pathtrace.cpp:1059-1068), which only rank 0 ever runs
+  if (cparams.samples != 1) cparams.samples = 1 << 30;
+  auto errors  = std::vector<std::string>(gpus);
+  auto workers = std::vector<std::thread>{};
+  for (int r = 1; r < gpus; r++) {
+    int share = sample_share(batch, gpus, r);
+    if (share <= 0) continue;
+    workers.emplace_back([&, r, share] {
+      auto& rep = *dev.replicas[r - 1];
+      if (vpt_cuda_set_device(rep.device) != VPT_OK ||
+          vpt_cuda_trace_samples(rep.scene, rep.state, &cparams, share) != VPT_OK)
+        errors[r] = vpt_cuda_last_error();
+    });
+  }
+  int status = vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams,
+      sample_share(batch, gpus, 0));
+  if (status != VPT_OK) errors[0] = vpt_cuda_last_error();
+  for (auto& w : workers) w.join();
+  for (auto& e : errors)
+    if (!e.empty()) throw std::runtime_error("vpt_cuda_trace_samples: " + e);
+  state.samples = vpt_cuda_state_total_samples(dev.state);
   dev.dirty = dev.dirty_rngs = true;
 }
 
@@ -370,15 +478,57 @@ void sync_state(pathtrace_state& state) {
   dev.dirty_rngs = false;
 }
 
+void reset_device_state(pathtrace_state& state, const std::vector<rng_state>& rngs,
+    uint64_t rng_offset) {
+  if (!state.device) state.device = std::make_shared<device_binding>();
+  auto& dev     = *state.device;
+  dev.base_rngs = rngs;
+  if (!dev.state) {
+    // no device state yet: restart the host copies (same O(log n) PCG32 jump as the device's)
+    state.rngs = rngs;
+    state.image.assign(state.image.size(), {0, 0, 0, 0});
+    for (auto& g : state.rngs) {
+      uint64_t cur_mult = 6364136223846793005ULL, cur_plus = g.inc, acc_mult = 1, acc_plus = 0;
+      for (auto delta = rng_offset; delta > 0; delta >>= 1) {
+        if (delta & 1) acc_mult *= cur_mult, acc_plus = acc_plus * cur_mult + cur_plus;
+        cur_plus = (cur_mult + 1) * cur_plus, cur_mult *= cur_mult;
+      }
+      g.state = acc_mult * g.state + acc_plus;
+    }
+    dev.rng_offset = rng_offset;
+    state.samples  = 0;
+    return;
+  }
+  check(vpt_cuda_reset_state(dev.state, (const uint64_t*)rngs.data()), "vpt_cuda_reset_state");
+  if (rng_offset) check(vpt_cuda_advance_rngs(dev.state, rng_offset), "vpt_cuda_advance_rngs");
+  dev.rng_offset = rng_offset;
+  int current    = vpt_cuda_current_device();
+  for (size_t r = 0; r < dev.replicas.size(); r++) {
+    auto& rep = *dev.replicas[r];
+    check(vpt_cuda_set_device(rep.device), "vpt_cuda_set_device");
+    auto a = vpt_cuda_reset_state(rep.state, (const uint64_t*)rngs.data());
+    auto b = a == VPT_OK ? vpt_cuda_advance_rngs(rep.state, rng_offset + rank_rng_offset((int)r + 1)) : a;
+    vpt_cuda_set_device(current);
+    check(b, "resetting a GPU replica");
+  }
+  state.samples = 0;
+  dev.dirty = dev.dirty_rngs = true;
+}
+
 void mark_host_stale(pathtrace_state& state) {
   if (state.device) state.device->dirty = state.device->dirty_rngs = true;
 }
 
 std::vector<uint8_t> get_render_srgb8(pathtrace_state& state) {
+  return get_render_tonemapped8(state, 0, false);
+}
+
+std::vector<uint8_t> get_render_tonemapped8(pathtrace_state& state, float exposure, bool filmic) {
   auto dstate = device_handle(state);
   if (!dstate) throw std::invalid_argument("nothing rendered yet");
   auto bytes = std::vector<uint8_t>((size_t)state.width * state.height * 4);
-  if (vpt_cuda_download_srgb8(dstate, state.samples, bytes.data(), bytes.size()) != VPT_OK)
+  if (vpt_cuda_download_tonemapped8(dstate, state.samples, exposure, filmic ? 1 : 0, bytes.data(),
+          bytes.size()) != VPT_OK)
     throw std::runtime_error(vpt_cuda_last_error());
   return bytes;
 }

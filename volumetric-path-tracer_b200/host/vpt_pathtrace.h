@@ -62,7 +62,20 @@ struct pathtrace_params {
   // device options (not in the reference)
   pathtrace_pipeline    pipeline            = pathtrace_pipeline::automatic;
   int                   batch               = 1;  // samples per pathtrace_samples call
+  // GPUs of this box to render on: every GPU holds the scene and a full
+  // accumulation image and takes a disjoint range of each call's samples; GPU r > 0 runs every
+  // pixel's PCG32 stream from r << 40 draws ahead; get_render sums the images on the first GPU
+  // (P2P over NVLink, vpt_cuda_state_add_peer). 1 GPU = the reference's streams exactly.
+  int                   gpus                = 1;
 };
+
+// Samples GPU `rank` of `gpus` takes out of a call of `batch` samples: contiguous ranges, the
+// first batch % gpus ranks one more (the C++ twin of sharding.sample_ranges).
+inline int sample_share(int batch, int gpus, int rank) {
+  return batch / gpus + (rank < batch % gpus ? 1 : 0);
+}
+// draws every pixel's generator of GPU `rank` is advanced by (PCG32 jump-ahead)
+inline uint64_t rank_rng_offset(int rank) { return (uint64_t)rank << 40; }
 
 inline const auto pathtrace_shader_names = std::vector<std::string>{"volpathtrace", "pathtrace",
     "naive", "eyelight", "normal", "texcoord", "color", "implicit", "implicit_normal"};
@@ -125,6 +138,9 @@ color_image get_render(const pathtrace_state& state);
 // Output stage on the device: get_render + rgb_to_srgb + float_to_byte (what save_image encodes
 // for 8-bit formats, yocto_sceneio.cpp:523-529); width*height*4 bytes, RGBA.
 std::vector<uint8_t> get_render_srgb8(pathtrace_state& state);
+// the same behind the display tonemap (tonemap(), yocto_color.h:306-316: exposure, filmic) that
+// the reference's viewer applies per frame (ypathtrace.cpp:159-189); bytes equal the reference's
+std::vector<uint8_t> get_render_tonemapped8(pathtrace_state& state, float exposure, bool filmic);
 void        get_render(color_image& render, const pathtrace_state& state);
 
 // The C-ABI scene description (include/vpt_cuda.h) of a host scene; the
@@ -165,6 +181,12 @@ void mark_device_dirty(pathtrace_state& state, int samples);
 // the device state was re-initialised behind the host mirrors' back (reset): image and
 // generators are downloaded again on the next sync
 void mark_host_stale(pathtrace_state& state);
+
+// Restart a render: the device image(s) are cleared and every generator is set to `rngs`
+// advanced by `rng_offset` draws (+ rank << 40 on the GPUs of a multi-GPU render); the host
+// mirrors are refreshed on the next sync. Before the first sample the host copies are restarted.
+void reset_device_state(pathtrace_state& state, const std::vector<rng_state>& rngs,
+    uint64_t rng_offset);
 
 // Device statistics of the last pathtrace_samples call on this state.
 vpt_trace_stats get_trace_stats(const pathtrace_state& state);
