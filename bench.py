@@ -21,6 +21,12 @@ K = 16 steps is exactly the config's 1024 spp. Mpaths/s = W*H*spp / seconds.
            do not bound this path (working set is L2-resident, no dense contraction).
   cpu_baseline / --impl reference: the UNMODIFIED reference CPU path (oracle/_ref/ref_render,
            parallel_for over all host cores) on a bounded sample of the same workload.
+  workloads short runs (--side-steps, default 3) of the other six tests/ scenes, so that one
+           driver-run line covers every configuration: value, e2e, whole-step roofline fraction and
+           (N = 1) the reference CPU baseline of each.
+  strong   BASELINE.json's split configurations (07_sdfunction 1920x800 4096 spp, 03_volume
+           1280x533 1024 spp): the TOTAL spp divided over the ranks, clock from scene upload to the
+           one download of the summed image. The driver derives efficiency from the per-N lines.
 Multi-GPU (torchrun): every rank renders the same image with a disjoint stretch of each
 pixel's random stream (weak scaling: per-GPU work fixed); the accumulation images are summed
 with one NCCL reduce. Time = max over ranks, measured on the device.
@@ -51,7 +57,20 @@ WORKLOADS = {
                        spp_per_step=16, size=(1280, 533)),
     "07_sdfunction": dict(scene="07_sdfunction", shader="implicit", resolution=1920, bounces=4,
                           spp_per_step=16, size=(1920, 800)),
+    # the two remaining tests/ scenes at the size of the reference's scripts/run.sh:2,4
+    "02_rollingteapot": dict(scene="02_rollingteapot", shader="pathtrace", resolution=720, bounces=4,
+                             spp_per_step=64, size=(720, 300)),
+    "04_head1": dict(scene="04_head1", shader="volpathtrace", resolution=720, bounces=4,
+                     spp_per_step=32, size=(720, 720)),
 }
+# what `data` says: tests/03_volume ships all its assets; the other six scenes lack meshes /
+# textures / grids in the reference checkout (.MISSING_LARGE_BLOBS) and run on deterministic
+# stand-ins (scenes/standins.py) inside the reference's own scene JSON
+DATA = {name: ("real: the reference's tests/03_volume scene as shipped" if name == "03_volume" else
+               "synthetic stand-in assets in the reference's scene JSON (scenes/standins.py)")
+        for name in WORKLOADS}
+# BASELINE.json configs the strong-scaling leg renders: total spp split over the GPUs
+STRONG = {"07_sdfunction": 4096, "03_volume": 1024}
 
 # Algorithmic work per camera path, measured with tests/hostsim (VPT_WORK_COUNTERS; identical
 # arithmetic to the kernels) at 360 px / 4 spp, and the FLOP cost of each unit.
@@ -68,6 +87,12 @@ WORK = {
     "07_sdfunction": dict(box_tests=0, tri_tests=0, inst_transforms=0, bounces=1.850,
                           sdf_scene_evals=129.25, sdf_fn_evals=595.43, sdf_grid_evals=259.04,
                           trilinear=14.94),
+    # hostsim with the binary tree (VPT_NO_WIDE=1): box tests after hoisting / instance culling,
+    # i.e. slightly BELOW the reference's own count, so these fractions are conservative
+    "02_rollingteapot": dict(box_tests=22.82, tri_tests=6.27, inst_transforms=5.96, bounces=1.968,
+                             sdf_scene_evals=0, sdf_fn_evals=0, sdf_grid_evals=0, trilinear=0),
+    "04_head1": dict(box_tests=30.67, tri_tests=4.26, inst_transforms=0.63, bounces=1.199,
+                     sdf_scene_evals=0, sdf_fn_evals=0, sdf_grid_evals=0, trilinear=0),
 }
 FLOPS = dict(box_tests=26, tri_tests=52, inst_transforms=30, bounces=300, sdf_scene_evals=0,
              sdf_fn_evals=45, sdf_grid_evals=43, trilinear=30)
@@ -82,10 +107,34 @@ EXTEND = {
     "01_surface": dict(box_tests=22.45, tri_tests=4.02, inst_transforms=4.90, prim_bytes=48),
     "05_head1ss": dict(box_tests=40.69, tri_tests=4.78, inst_transforms=0.62, prim_bytes=48),
 }
-# dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend_persistent
-# launch (one of the two pipes: 341 k rays), from profiles/r01d_ncu_full.brief.txt (ncu --set full),
-# per launch like `achieved`
-NCU_TRAFFIC = {"03_volume": 46.1e6 + 6.7e6}
+def ncu_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one full-occupancy k_wf_extend_persistent
+    launch (one of the two pipes), read from the NEWEST committed ncu --set full brief under
+    profiles/ (scripts/ncu_brief.py output of the 03_volume capture). -> (bytes, file) or (None, None)"""
+    if workload != "03_volume":
+        return None, None
+    import glob
+
+    best = None
+    for path in glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full*.brief.txt")):
+        if "sdf" in os.path.basename(path):
+            continue
+        try:
+            lines = open(path).read().splitlines()
+            cols = lines[0].split()[1:]
+            col = next(i for i, c in enumerate(cols) if c.startswith("k_wf_extend_persistent"))
+            val = {}
+            for ln in lines[1:]:
+                for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    if ln.startswith(key):
+                        unit = ln[ln.index("[") + 1:ln.index("]")]
+                        scale = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}[unit]
+                        val[key] = float(ln[60:].split()[col]) * scale
+            if len(val) == 2 and (best is None or os.path.basename(path) > os.path.basename(best[1])):
+                best = (val["dram__bytes_read.sum"] + val["dram__bytes_write.sum"], path)
+        except Exception:
+            continue
+    return (best[0], os.path.relpath(best[1], ROOT)) if best else (None, None)
 
 
 def extend_flops_per_ray(name):
@@ -184,11 +233,17 @@ def reference_arm(args, wl, rank):
     total = sum(times)
     value = info["paths"] * len(times) / total / 1e6
     sample = f"{spp} spp of {info['size'][0]}x{info['size'][1]} per step ({info['paths']} paths)"
+    config = workload_config(args, wl)
+    # the bounded sample this arm really runs per step (throughput per path does not depend on
+    # spp: the reference does one parallel_for barrier per sample)
+    config["spp_per_step"] = spp
+    config["paths_per_step_per_gpu"] = info["paths"]
+    config["workload"] += f" [reference arm: {spp} spp per step]"
     line = {"impl": "reference", "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * total / len(times), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, wl),
+            "vs_baseline": None, "dtype": "f32", "data": DATA[args.workload],
+            "config": config,
             "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": info["threads"],
                              "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0,
@@ -209,67 +264,108 @@ def workload_config(args, wl):
             "parallelism": f"sample-range x{args.gpus}, one NCCL reduce"}
 
 
-def gpu_arm(args, wl, rank, world, local_rank):
-    import numpy as np
-    import torch
+class Bench:
+    """Shared plumbing of the GPU arm: package, device, process group, L2 flush buffer."""
 
-    import __graft_entry__ as entry
+    def __init__(self, args, rank, world, local_rank):
+        import torch
 
-    pkg = entry.load_package()
-    b = pkg.binding
-    if not torch.cuda.is_available() or b.device_count() < 1:
-        raise SystemExit("bench.py needs a CUDA device: the B200 path has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    b.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
+        import __graft_entry__ as entry
 
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        self.args, self.rank, self.world, self.local_rank = args, rank, world, local_rank
+        self.torch = torch
+        self.pkg = entry.load_package()
+        self.b = self.pkg.binding
+        if not torch.cuda.is_available() or self.b.device_count() < 1:
+            raise SystemExit("bench.py needs a CUDA device: the B200 path has no CPU fallback")
+        torch.cuda.set_device(local_rank)
+        self.b.set_device(local_rank)
+        self.dist = None
+        if world > 1:
+            import torch.distributed as dist
 
-    scene_path = os.path.join(ROOT, "scenes", "_built", wl["scene"] + ".vptscene")
-    if not os.path.exists(scene_path):
-        raise SystemExit(f"{scene_path} is missing: run __graft_entry__.build() where the reference is")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            self.dist = dist
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        self.rng_offset = self.pkg.sharding.rank_rng_offset(rank)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, values):
+        t = self.torch.tensor(values, dtype=self.torch.float64, device="cuda")
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(v) for v in t.tolist()]
+
+    def reduce_to_rank0(self, r, total_samples):
+        """The one collective of the path: sum of the accumulation images on rank 0 (NCCL)."""
+        if self.dist is None:
+            return 0.0
+        torch = self.torch
+        acc = torch.empty(r.height * r.width * 4, dtype=torch.float32, device="cuda")
+        r.export_image(acc.data_ptr())
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        self.pkg.sharding.reduce_images(acc, dst=0)
+        e1.record()
+        torch.cuda.synchronize()
+        if self.rank == 0:
+            r.import_image(acc.data_ptr(), total_samples)
+        return e0.elapsed_time(e1)
+
+    def scene(self, name):
+        path = os.path.join(ROOT, "scenes", "_built", WORKLOADS[name]["scene"] + ".vptscene")
+        if not os.path.exists(path):
+            raise SystemExit(f"{path} is missing: run __graft_entry__.build() where the reference is")
+        t0 = time.time()
+        sc = self.b.Scene(path)
+        return sc, time.time() - t0
+
+
+def fp32_peak():
+    sm_max = float(measured_peaks().get("sm_max_mhz", 1965.0))
+    return SM_COUNT * FP32_LANES * 2 * sm_max * 1e6 / 1e12
+
+
+def measure(bn, name, steps, warmup, full):
+    """Device-resident value, end-to-end value and whole-step roofline fraction of one workload.
+    `full`: the headline run (clock sampling, per-launch roofline of the dominant kernel)."""
+    args, b, torch, np = bn.args, bn.b, bn.torch, __import__("numpy")
+    wl = WORKLOADS[name]
     spp = wl["spp_per_step"]
-    total_spp = (args.warmup + args.steps) * spp + 2
-    t0 = time.time()
-    scene = b.Scene(scene_path)
-    host_build_s = time.time() - t0
-    params = b.make_params(shader=wl["shader"], samples=total_spp, resolution=wl["resolution"],
-                           bounces=wl["bounces"], pipeline=args.pipeline)
+    scene, host_build_s = bn.scene(name)
+    params = b.make_params(shader=wl["shader"], samples=(warmup + steps) * spp + 2,
+                           resolution=wl["resolution"], bounces=wl["bounces"], pipeline=args.pipeline)
     r = b.Render(scene, params)
     # sample-range sharding: rank r owns a disjoint stretch of every pixel's PCG32 stream
-    rng_offset = pkg.sharding.rank_rng_offset(rank)
-    r.reset(rng_offset)
+    r.reset(bn.rng_offset)
     paths_per_step = r.width * r.height * spp
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     t0 = time.time()
     r.trace(1)  # first call uploads the scene
     upload_s = time.time() - t0
-    r.reset(rng_offset)
-    for _ in range(args.warmup):
+    r.reset(bn.rng_offset)
+    for _ in range(warmup):
         r.trace(spp)
-    if dist is not None:
+    if full and bn.dist is not None:
         # warm-up of the one collective too (NCCL sets up its channels on first use)
         scratch = torch.zeros(r.height * r.width * 4, dtype=torch.float32, device="cuda")
-        pkg.sharding.reduce_images(scratch, dst=0)
+        bn.pkg.sharding.reduce_images(scratch, dst=0)
         del scratch
 
     # ---- device-resident timed region ------------------------------------------------------
-    barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    step_ms, launches = [], 0
+    bn.barrier()
+    sampler = ClockSampler(bn.local_rank) if full else None
+    if sampler:
+        sampler.start()
+    step_ms, launches, graphs = [], 0, 0
     top_ms, top_units, top_launches = 0.0, 0, 0
-    for _ in range(args.steps):
-        flush.zero_()
+    for _ in range(steps):
+        bn.flush.zero_()
         torch.cuda.synchronize()
         r.trace(spp)
         st = r.stats()
@@ -278,120 +374,164 @@ def gpu_arm(args, wl, rank, world, local_rank):
         top_units += st.top_kernel_units
         top_launches += st.top_kernel_launches
         launches += st.kernel_launches
-    barrier()
-    clocks = sampler.summary()
+        graphs += st.graph_launches
+    bn.barrier()
+    clocks = sampler.summary() if sampler else None
     total_ms = float(sum(step_ms))
 
     # ---- one reduce of the accumulation images (NCCL over NVLink) ---------------------------
-    reduce_ms = 0.0
-    image_mean = None
     done_spp = r.samples
-    if dist is not None:
-        acc = torch.empty(r.height * r.width * 4, dtype=torch.float32, device="cuda")
-        r.export_image(acc.data_ptr())
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        pkg.sharding.reduce_images(acc, dst=0)
-        e1.record()
-        torch.cuda.synchronize()
-        reduce_ms = e0.elapsed_time(e1)
-        if rank == 0:
-            r.import_image(acc.data_ptr(), done_spp * world)
-    if rank == 0:
+    reduce_ms = bn.reduce_to_rank0(r, done_spp * bn.world)
+    image_mean = None
+    if bn.rank == 0:
         img = r.image(normalized=True)
         image_mean = float(np.clip(img[..., :3], 0, 4).mean())
 
-    # ---- end to end through the host API with host buffers ------------------------------------
-    e2e_steps = max(1, min(args.steps, 8))
-    barrier()
+    # ---- end to end through the host API with host buffers -----------------------------------
+    # per step: generators up from pinned host memory, trace, (N > 1: the NCCL reduce,) the
+    # accumulation image down to the host
+    e2e_steps = max(1, min(steps, 8))
+    bn.barrier()
     t0 = time.time()
     for _ in range(e2e_steps):
-        r.reset(rng_offset)          # H2D: per-pixel generators from (pinned) host memory
+        r.reset(bn.rng_offset)          # H2D
         r.trace(spp)
-        host_img = r.image(normalized=False)  # D2H: the accumulation image
+        bn.reduce_to_rank0(r, spp * bn.world)
+        host_img = r.image(normalized=False)  # D2H
     torch.cuda.synchronize()
     e2e_s = time.time() - t0
     del host_img
     pix = r.width * r.height
 
-    # ---- the dominant kernel on its own (untimed extra call, one pipe) ---------------------------
-    # In the timed region two wavefront pipes share the device, so the event pair around an extend
-    # launch also spans the other pipe's kernels. One more call with a single pipe gives the
-    # kernel's own rate; it is reported beside the timed-region figure, never instead of it.
+    # ---- the dominant kernel on its own (untimed extra call, one pipe) ------------------------
     alone = None
-    if rank == 0 and "VPT_WF_PIPES" not in os.environ:
+    if full and bn.rank == 0 and "VPT_WF_PIPES" not in os.environ:
         os.environ["VPT_WF_PIPES"] = "1"
-        r.reset(rng_offset)
+        r.reset(bn.rng_offset)
         r.trace(spp)
         st = r.stats()
         del os.environ["VPT_WF_PIPES"]
         if st.top_kernel_launches > 0 and st.top_kernel_ms > 0:
             alone = (st.top_kernel_ms, st.top_kernel_units, st.top_kernel_launches)
+    r.close()
+    scene.close()
 
-    # ---- max over ranks -----------------------------------------------------------------------
-    times = torch.tensor([total_ms + reduce_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    worst_ms, worst_e2e_ms = (float(v) for v in times.tolist())
+    worst_ms, worst_e2e_ms = bn.max_over_ranks([total_ms + reduce_ms, e2e_s * 1e3])
+    value = bn.world * paths_per_step * steps / (worst_ms / 1e3) / 1e6
+    e2e_value = bn.world * paths_per_step * e2e_steps / (worst_e2e_ms / 1e3) / 1e6
+    ms_per_step = worst_ms / steps
+    fpp = flops_per_path(name)
+    step_tflops = fpp * paths_per_step / (ms_per_step / 1e3) / 1e12
+    return dict(value=value, e2e_value=e2e_value, e2e_steps=e2e_steps, ms_per_step=ms_per_step,
+                step_tflops=step_tflops, fpp=fpp, launches=launches, graphs=graphs, clocks=clocks,
+                top=(top_ms, top_units, top_launches), alone=alone, reduce_ms=reduce_ms,
+                image_mean=image_mean, host_build_s=host_build_s, upload_s=upload_s, pix=pix,
+                size=(wl["size"][0], wl["size"][1]), paths_per_step=paths_per_step)
 
+
+def strong_leg(bn, name, total_spp):
+    """BASELINE.json's split configuration: `total_spp` samples of the whole image divided over
+    the ranks (rank r renders sample_ranges[r] from its own stretch of the streams), clock =
+    scene upload to the device + first (cold) call + render + the NCCL reduce + ONE download of
+    the summed image on rank 0; scene file load and host BVH / light builds are outside."""
+    args, b, torch = bn.args, bn.b, bn.torch
+    wl = WORKLOADS[name]
+    scene, host_build_s = bn.scene(name)
+    first, mine = bn.pkg.sharding.sample_ranges(total_spp, bn.world)[bn.rank]
+    params = b.make_params(shader=wl["shader"], samples=max(mine, 2), resolution=wl["resolution"],
+                           bounces=wl["bounces"], pipeline=args.pipeline)
+    r = b.Render(scene, params)
+    r.reset(bn.rng_offset)
+    bn.barrier()
+    t0 = time.time()
+    done = 0
+    while done < mine:
+        n = min(64, mine - done)
+        r.trace(n)  # the first call uploads the scene
+        done += n
+    bn.reduce_to_rank0(r, total_spp)
+    if bn.rank == 0:
+        img = r.image(normalized=False)
+        del img
+    torch.cuda.synchronize()
+    seconds = time.time() - t0
+    (worst,) = bn.max_over_ranks([seconds])
+    paths = wl["size"][0] * wl["size"][1] * total_spp
+    r.close()
+    scene.close()
+    return {"workload": f"tests/{wl['scene']} {wl['shader']} {wl['size'][0]}x{wl['size'][1]} "
+                        f"{total_spp} spp in total",
+            "n_gpus": bn.world, "spp_total": total_spp, "spp_this_rank": mine,
+            "seconds": worst, "value": paths / worst / 1e6, "unit": "Mpaths/s", "scaling": "strong",
+            "clock": "scene upload + cold first call + render + NCCL reduce + one D2H of the sum; "
+                     "max over ranks (wall clock around blocking calls)"}
+
+
+def roofline_block(name, m, wl):
+    """north_star's compute roofline: FP32 peak / algorithmic flops (HBM and tensor cores do not
+    bound this path). Dominant kernel timed live with CUDA events on its own stream."""
+    peak = fp32_peak()
+    top_ms, top_units, top_launches = m["top"]
+    wavefront = extend_flops_per_ray(name) is not None and top_launches > 0 and top_ms > 0 \
+        and wl["shader"] in ("volpathtrace", "pathtrace", "naive")
+    traffic, traffic_src = ncu_traffic(name) if wavefront else (None, None)
+    if wavefront:
+        kernel = "k_wf_extend_persistent"
+        achieved = extend_flops_per_ray(name) * top_units / (top_ms / 1e3) / 1e12
+        per_launch = {"kernel": kernel, "sampled_launches": top_launches,
+                      "avg_launch_us": 1e3 * top_ms / top_launches,
+                      "avg_rays_per_launch": top_units / top_launches,
+                      "grays_per_s": top_units / (top_ms / 1e3) / 1e9,
+                      "flops_per_ray": extend_flops_per_ray(name),
+                      "algorithmic_bytes_per_ray": extend_bytes_per_ray(name),
+                      "note": "timed region: the other wavefront pipe's kernels share the device "
+                              "during these launches"}
+        if m["alone"] is not None:
+            a_ms, a_units, a_n = m["alone"]
+            a_tflops = extend_flops_per_ray(name) * a_units / (a_ms / 1e3) / 1e12
+            per_launch["alone"] = {"sampled_launches": a_n, "avg_launch_us": 1e3 * a_ms / a_n,
+                                   "avg_rays_per_launch": a_units / a_n,
+                                   "grays_per_s": a_units / (a_ms / 1e3) / 1e9,
+                                   "achieved": a_tflops, "frac": a_tflops / peak,
+                                   "note": "one untimed extra call with a single pipe "
+                                           "(VPT_WF_PIPES=1): the kernel with the device to itself"}
+    else:
+        kernel, achieved, per_launch = "whole step", m["step_tflops"], None
+    return {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+            "kernel": kernel, "per_launch": per_launch,
+            "whole_step": {"achieved": m["step_tflops"], "frac": m["step_tflops"] / peak,
+                           "flops_per_path": m["fpp"]},
+            "note": "compute roofline of north_star (FP32 peak / algorithmic flops; HBM and tensor "
+                    "cores do not bound this path): algorithmic work = the reference algorithm's, "
+                    "from tests/hostsim counters; peak = 148 SM x 128 lanes x 2 x sm_max_mhz of "
+                    "MEASURED_PEAKS.json, which holds no fp32 figure; traffic = ncu dram bytes of "
+                    "one full-occupancy launch, read from the newest profiles/*brief.txt"}
+
+
+def gpu_arm(args, wl, rank, world, local_rank):
+    bn = Bench(args, rank, world, local_rank)
+    m = measure(bn, args.workload, args.steps, args.warmup, full=True)
+    line = None
     if rank == 0:
-        value = world * paths_per_step * args.steps / (worst_ms / 1e3) / 1e6
-        e2e_value = world * paths_per_step * e2e_steps / (worst_e2e_ms / 1e3) / 1e6
-        peaks = measured_peaks()
-        sm_max = float(peaks.get("sm_max_mhz", 1965.0))
-        fp32_peak = SM_COUNT * FP32_LANES * 2 * sm_max * 1e6 / 1e12
-        fpp = flops_per_path(args.workload)
-        ms_per_step = worst_ms / args.steps
-        step_tflops = fpp * paths_per_step / (ms_per_step / 1e3) / 1e12
-        wavefront = args.pipeline != "mega" and extend_flops_per_ray(args.workload) is not None \
-            and top_launches > 0 and wl["shader"] in ("volpathtrace", "pathtrace", "naive")
-        if wavefront:
-            # dominant kernel, timed live with CUDA events on its own stream (one launch per
-            # counter poll, ray count known exactly): flops per ray x rays / duration
-            kernel = "k_wf_extend_persistent"
-            achieved = extend_flops_per_ray(args.workload) * top_units / (top_ms / 1e3) / 1e12
-            per_launch = {"kernel": kernel, "sampled_launches": top_launches,
-                          "avg_launch_us": 1e3 * top_ms / top_launches,
-                          "avg_rays_per_launch": top_units / top_launches,
-                          "grays_per_s": top_units / (top_ms / 1e3) / 1e9,
-                          "flops_per_ray": extend_flops_per_ray(args.workload),
-                          "algorithmic_bytes_per_ray": extend_bytes_per_ray(args.workload),
-                          "note": "timed region: the other wavefront pipe's kernels share the device "
-                                  "during these launches"}
-            if alone is not None:
-                a_ms, a_units, a_n = alone
-                a_tflops = extend_flops_per_ray(args.workload) * a_units / (a_ms / 1e3) / 1e12
-                per_launch["alone"] = {"sampled_launches": a_n, "avg_launch_us": 1e3 * a_ms / a_n,
-                                       "avg_rays_per_launch": a_units / a_n,
-                                       "grays_per_s": a_units / (a_ms / 1e3) / 1e9,
-                                       "achieved": a_tflops, "frac": a_tflops / fp32_peak,
-                                       "note": "one untimed extra call with a single pipe "
-                                               "(VPT_WF_PIPES=1): the kernel with the device to itself"}
-        else:
-            kernel, achieved, per_launch = "whole step", step_tflops, None
         line = {
-            "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "metric": "Mpaths/s", "value": m["value"], "unit": "Mpaths/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": m["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, wl),
-            "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": pix * 16,
-                    "d2h_bytes_per_step": pix * 16, "steps": e2e_steps},
-            "gpu_launches": launches,
-            "clocks": clocks,
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak,
-                         "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                         "traffic": NCU_TRAFFIC.get(args.workload) if wavefront else None,
-                         "kernel": kernel, "per_launch": per_launch,
-                         "whole_step": {"achieved": step_tflops, "frac": step_tflops / fp32_peak,
-                                        "flops_per_path": fpp},
-                         "note": "compute roofline of north_star (FP32 peak / algorithmic flops; "
-                                 "HBM and tensor cores do not bound this path): algorithmic work from "
-                                 "tests/hostsim counters; peak = 148 SM x 128 lanes x 2 x sm_max_mhz "
-                                 "of MEASURED_PEAKS.json, which holds no fp32 figure; traffic = ncu "
-                                 "dram bytes of one full-occupancy launch (profiles/)"},
-            "reduce_ms": reduce_ms, "image_mean": image_mean,
-            "host_build_s": host_build_s, "scene_upload_s": upload_s,
+            "data": DATA[args.workload], "config": workload_config(args, wl),
+            "e2e": {"value": m["e2e_value"], "unit": "Mpaths/s", "h2d_bytes_per_step": m["pix"] * 16,
+                    "d2h_bytes_per_step": m["pix"] * 16, "steps": m["e2e_steps"],
+                    "includes": "generator upload, trace, " + ("NCCL reduce, " if world > 1 else "") +
+                                "accumulation image download"},
+            "gpu_launches": m["launches"],
+            "host_submissions": {"graph_launches": m["graphs"],
+                                 "kernels_inside_graphs": m["graphs"] * 40,
+                                 "note": "gpu_launches counts every kernel executed; a batch of 8 "
+                                         "iterations (40 kernels) reaches the device as one CUDA "
+                                         "graph launch"},
+            "clocks": m["clocks"], "roofline": roofline_block(args.workload, m, wl),
+            "reduce_ms": m["reduce_ms"], "image_mean": m["image_mean"],
+            "host_build_s": m["host_build_s"], "scene_upload_s": m["upload_s"],
         }
         if world == 1 and not args.no_cpu_baseline:
             info = run_reference_cpu(wl, 8)
@@ -401,12 +541,45 @@ def gpu_arm(args, wl, rank, world, local_rank):
                     "kind": "reference",
                     "sample": f"8 spp of {info['size'][0]}x{info['size'][1]} ({info['paths']} paths, "
                               f"{info['seconds']:.2f} s) by oracle/_ref/ref_render"}
+    # ---- the other configurations, short runs (so that the driver's record covers them) ----------
+    if not args.no_workloads:
+        others = {}
+        for name in WORKLOADS:
+            if name == args.workload:
+                continue
+            scene_file = os.path.join(ROOT, "scenes", "_built", WORKLOADS[name]["scene"] + ".vptscene")
+            if not os.path.exists(scene_file):
+                continue
+            w = measure(bn, name, args.side_steps, 1, full=False)
+            if rank == 0:
+                entry = {"value": w["value"], "unit": "Mpaths/s", "ms_per_step": w["ms_per_step"],
+                         "steps": args.side_steps, "e2e": w["e2e_value"],
+                         "frac": w["step_tflops"] / fp32_peak(), "achieved_tflops": w["step_tflops"],
+                         "gpu_launches": w["launches"], "data": DATA[name],
+                         "workload": workload_config(args, WORKLOADS[name])["workload"]}
+                if world == 1 and not args.no_cpu_baseline:
+                    info = run_reference_cpu(WORKLOADS[name], 2)
+                    if info is not None:
+                        entry["cpu_baseline"] = {"value": info["mpaths"], "unit": "Mpaths/s",
+                                                 "cores": info["threads"], "kind": "reference",
+                                                 "sample": f"2 spp, {info['seconds']:.2f} s"}
+                others[name] = entry
+        if rank == 0:
+            line["workloads"] = others
+    # ---- strong scaling: BASELINE.json's split configurations --------------------------------
+    if not args.no_strong:
+        strong = {}
+        for name, total_spp in STRONG.items():
+            scene_file = os.path.join(ROOT, "scenes", "_built", WORKLOADS[name]["scene"] + ".vptscene")
+            if os.path.exists(scene_file):
+                strong[name] = strong_leg(bn, name, total_spp)
+        if rank == 0:
+            line["strong"] = strong
+    if rank == 0:
         print(json.dumps(line), flush=True)
-    r.close()
-    scene.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if bn.dist is not None:
+        bn.dist.barrier()
+        bn.dist.destroy_process_group()
     return 0
 
 
@@ -419,6 +592,9 @@ def main():
     ap.add_argument("--workload", default="03_volume", choices=sorted(WORKLOADS))
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true", help="skip the short runs of the other scenes")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg")
+    ap.add_argument("--side-steps", type=int, default=3)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     wl = WORKLOADS[args.workload]

@@ -221,6 +221,8 @@ typedef struct vpt_trace_stats {
   uint64_t rays_lightpdf;   /* instance-targeted traversals */
   uint64_t sdf_evals;       /* scene sdf evaluations */
   uint64_t top_kernel_units; /* rays (paths for the megakernel) those sampled launches processed */
+  uint64_t graph_launches;   /* batches (8 iterations = 40 of the kernel_launches) that the host
+                                submitted as ONE CUDA graph launch instead of kernel by kernel */
 } vpt_trace_stats;
 
 int  vpt_cuda_device_count(void);

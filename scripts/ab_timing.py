@@ -17,5 +17,5 @@ for _ in range(calls):
     ms.append(st.device_ms)
 med = statistics.median(ms)
 print(f"{scene} {shader} {r.width}x{r.height} b{bounces} {spp} spp: median {med:.1f} ms (min {min(ms):.1f}, max {max(ms):.1f}) "
-      f"-> {r.width * r.height * spp / med / 1e3:.1f} Mpaths/s; {st.kernel_launches} launches; "
+      f"-> {r.width * r.height * spp / med / 1e3:.1f} Mpaths/s; {st.kernel_launches} kernels, {st.graph_launches} graph launches; "
       f"tag={os.environ.get('VPT_LIB_DIR', '')} {' '.join(k + '=' + v for k, v in os.environ.items() if k.startswith("VPT_"))}", flush=True)

@@ -7,13 +7,10 @@ set -x
 TAG=${1:-r01d}
 O=gpurun_out
 python bench.py > $O/${TAG}_bench_1gpu_03_volume.json 2> $O/${TAG}_bench_03_volume.err
-for w in 01_surface 05_head1ss 06_gridsdf 07_sdfunction; do
-  python bench.py --workload $w --steps 8 --warmup 3 > $O/${TAG}_bench_1gpu_$w.json 2> $O/${TAG}_bench_$w.err
-done
 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_reference_arm.json 2>> $O/${TAG}_bench_03_volume.err
 ncu --metrics gpu__time_duration.sum,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum \
   --clock-control none -c 9000 --csv --log-file $O/${TAG}_launches_bench.csv \
-  python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $O/${TAG}_ncu_launches.log 2>&1
+  python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-workloads --no-strong > $O/${TAG}_ncu_launches.log 2>&1
 ncu --set full --import-source on --clock-control none --launch-skip 130 --launch-count 8 -f \
   -o $O/${TAG}_ncu_full python scripts/profile_step.py 03_volume volpathtrace 1280 64 16 > $O/${TAG}_ncu_full.log 2>&1
 ls -la $O

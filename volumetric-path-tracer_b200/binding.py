@@ -45,7 +45,7 @@ class TraceStats(C.Structure):
                 ("kernel_launches", C.c_int32), ("top_kernel_launches", C.c_int32),
                 ("paths", C.c_uint64), ("rays_extend", C.c_uint64),
                 ("rays_lightpdf", C.c_uint64), ("sdf_evals", C.c_uint64),
-                ("top_kernel_units", C.c_uint64)]
+                ("top_kernel_units", C.c_uint64), ("graph_launches", C.c_uint64)]
 
 
 class LightsStats(C.Structure):

@@ -217,7 +217,7 @@ constexpr int wide_none = (int)0x80000001;  // "this BVH has no wide nodes" (nev
 VPT_FN constexpr int make_ref(int payload, int tag) { return ~((payload << 2) | tag); }
 constexpr int leaf_start_limit = 1 << 26;  // f4 index of a leaf's first primitive record
 #if !defined(VPT_TRAV_POPS)
-#define VPT_TRAV_POPS 8
+#define VPT_TRAV_POPS 4
 #endif
 constexpr int trav_pops = VPT_TRAV_POPS;
 

@@ -40,6 +40,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <memory>
 #include <vector>
 #include <cuda_runtime.h>
@@ -58,6 +59,7 @@ constexpr int wf_block   = 128;
 constexpr int wf_pipes   = VPT_WF_PIPES;        // independent wavefronts (streams) per render call
 constexpr int wf_pipes_min_slots = 1 << 16;  // smaller images run one pipe
 constexpr int wf_batch   = 8;  // iterations enqueued between two looks at the counters
+constexpr int wf_timed_every = 4;  // with graphs: every 4th batch of pipe 0 carries the timed extend
 constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped), last: suspended
 constexpr int wf_class_susp = wf_classes - 1;
 
@@ -130,6 +132,11 @@ struct wf_pipe {
   cudaEvent_t  poll[2] = {nullptr, nullptr};
   int*         queues = nullptr;
   size_t       susp_bytes = 0;
+  // one batch of wf_batch iterations as a CUDA graph (kernel arguments are baked in: `graph_key`
+  // holds their bytes, a different scene / state / shader / size re-captures)
+  static constexpr int graph_classes = 7;  // grids of full, 1/2, ... 1/64 of the pipe's slots
+  cudaGraphExec_t   graph[graph_classes] = {};
+  std::vector<char> graph_key[graph_classes];
   // host-side progress
   int active = 0, cur = 0, inflight = 0, batches = 0;
   int polled_cur[2] = {0, 0};
@@ -155,6 +162,8 @@ struct wavefront_buffers {
         if (p.host_counters[i]) cudaFreeHost(p.host_counters[i]);
         if (p.poll[i]) cudaEventDestroy(p.poll[i]);
       }
+      for (auto g : p.graph)
+        if (g) cudaGraphExecDestroy(g);
       if (p.stream) cudaStreamDestroy(p.stream);
     }
     if (k0) cudaEventDestroy(k0);
@@ -953,6 +962,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   }
 #endif
   *launches = 0;
+  int graph_count = 0, *graph_launches = &graph_count;
   // the first extend launch of every batch of pipe 0 is timed with CUDA events: its ray count
   // is known exactly, so the pairs give the dominant kernel's rays per second (with two
   // pipes the other pipe's kernels share the device during that time, as they do in the run)
@@ -976,30 +986,92 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
 
   // one batch = wf_batch iterations, then a snapshot of the counters; two batches per pipe
   // are kept in flight so that a stream never runs dry while the host reads a snapshot
+  // the 5 kernels of one iteration at grid `grid` (extend: at most the resident set)
+  auto iteration = [&](wf_pipe& p, int grid, bool timed) {
+    auto& w = p.view;
+    if (timed) cudaEventRecord(wf.k0, p.stream);
+    if (trace) trace->mark(grid);
+    if (persistent)
+      k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
+          scene.d, prm, w, p.cur, suspend_at);
+    else
+      k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+    if (timed) cudaEventRecord(wf.k1, p.stream);
+    k_wf_sort<<<grid, wf_block, 0, p.stream>>>(w, p.cur);
+    if (trace) trace->mark(grid);
+    k_wf_shade<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
+    if (trace) trace->mark(grid);
+    k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+    k_wf_pdf_tail<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
+    if (trace) trace->mark(grid);
+    p.cur ^= 1;
+  };
+  // A batch as ONE graph launch. Every kernel reads its true work count from device memory
+  // and a block without work exits at once, so a graph captured at a grid no smaller than the
+  // batch needs can be replayed for any batch (of this call and of later calls on the same
+  // scene / state). Graphs are captured lazily for grids of 1, 1/2, ... 1/64 of the pipe's
+  // slots and a batch takes the smallest that covers its active slots (B200: with the full
+  // grid alone the ~200 tail iterations of 03_volume paid 3 ms for empty blocks). The host
+  // submits 1 graph + 1 counter copy per batch instead of 40 kernels. The batch that
+  // carries the timed extend launch (one in wf_timed_every on pipe 0) is enqueued kernel by
+  // kernel, as before. wf_batch is even, so every batch starts on queue parity 0.
+  static_assert(wf_batch % 2 == 0, "a graph assumes every batch starts on the same queue parity");
+  auto batch_graph = [&](int i, int need) -> cudaGraphExec_t {
+    auto& p = wf.pipe[i];
+    struct key_t {
+      DScene d; DParams prm; wf_view view; f4* image; rng_t* rngs;
+      int suspend_at, resident, grid, shader, persistent; size_t smem;
+    } key;
+    memset(&key, 0, sizeof(key));
+    int full = (wavefront_buffers::pipe_slots(slots, npipes, i) + wf_block - 1) / wf_block;
+    int cls  = 0;
+    while (cls + 1 < wf_pipe::graph_classes && ((full + (2 << cls) - 1) >> (cls + 1)) >= need) cls++;
+    full = (full + (1 << cls) - 1) >> cls;
+    if (full < need) return nullptr;
+    key.d = scene.d, key.prm = prm, key.view = p.view, key.image = image, key.rngs = rngs;
+    key.suspend_at = suspend_at, key.resident = resident, key.grid = full, key.shader = S;
+    key.persistent = persistent, key.smem = smem;
+    auto& exec = p.graph[cls];
+    auto& kept = p.graph_key[cls];
+    if (exec && kept.size() == sizeof(key) && !memcmp(kept.data(), &key, sizeof(key))) return exec;
+    if (exec) cudaGraphExecDestroy(exec), exec = nullptr;
+    if (p.cur != 0) return nullptr;
+    cudaGraph_t g = nullptr;
+    if (cudaStreamBeginCapture(p.stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    for (int it = 0; it < wf_batch; it++) iteration(p, full, false);
+    auto e = cudaStreamEndCapture(p.stream, &g);
+    if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, g, 0);
+    if (g) cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      exec = nullptr;
+      return nullptr;
+    }
+    kept.assign((const char*)&key, (const char*)&key + sizeof(key));
+    return exec;
+  };
+  const char* graph_env = getenv("VPT_WF_GRAPH");  // 0: kernel-by-kernel submission everywhere
+  bool use_graph = !(graph_env && atoi(graph_env) == 0) && !trace;
+
+  // one batch = wf_batch iterations, then a snapshot of the counters; two batches per pipe
+  // are kept in flight so that a stream never runs dry while the host reads a snapshot
   auto enqueue = [&](int i) -> cudaError_t {
     auto& p    = wf.pipe[i];
     auto& w    = p.view;
     int   grid = (p.active + wf_block - 1) / wf_block;
-    bool  timed = i == 0 && !timed_pending;
-    for (int it = 0; it < wf_batch; it++) {
-      if (it == 0 && timed) cudaEventRecord(wf.k0, p.stream);
-      if (trace) trace->mark(grid);
-      if (persistent)
-        k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
-            scene.d, prm, w, p.cur, suspend_at);
-      else
-        k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
-      if (it == 0 && timed) cudaEventRecord(wf.k1, p.stream);
-      k_wf_sort<<<grid, wf_block, 0, p.stream>>>(w, p.cur);
-      if (trace) trace->mark(grid);
-      k_wf_shade<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
-      if (trace) trace->mark(grid);
-      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
-      k_wf_pdf_tail<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
-      if (trace) trace->mark(grid);
-      p.cur ^= 1;
-      *launches += 5;
+    bool  timed = i == 0 && !timed_pending && (!use_graph || p.batches % wf_timed_every == 0);
+    auto  exec  = use_graph && !timed && p.cur == 0 ? batch_graph(i, grid) : nullptr;
+    if (exec) {
+      auto e = cudaGraphLaunch(exec, p.stream);
+      if (e != cudaSuccess) return e;
+      *graph_launches += 1;
+    } else {
+      for (int it = 0; it < wf_batch; it++) iteration(p, grid, it == 0 && timed);
     }
+    *launches += 5 * wf_batch;
     if (timed) timed_pending = true, timed_active = p.active, timed_batch = p.batches;
     int  k = p.batches & 1;
     auto e = cudaMemcpyAsync(p.host_counters[k], w.counters, sizeof(wf_counters),
@@ -1064,6 +1136,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   stats->top_kernel_ms       = (float)top_ms;
   stats->top_kernel_launches = top_launches;
   stats->top_kernel_units    = top_rays;
+  stats->graph_launches      = (uint64_t)graph_count;
   stats->rays_extend = stats->rays_lightpdf = 0;
   for (int i = 0; i < npipes; i++) {
     if (wf.pipe[i].batches == 0) continue;  // a pipe without slots never wrote its counters
