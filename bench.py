@@ -516,6 +516,8 @@ def gpu_arm(args, wl, rank, world, local_rank):
     if rank == 0:
         line = {
             "metric": "Mpaths/s", "value": m["value"], "unit": "Mpaths/s", "n_gpus": world,
+            "build": "fast (statistical parity)" if os.path.basename(os.environ.get("VPT_LIB_DIR", "")) == "fast"
+                     else "exact (bit-identical to the reference)",
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": m["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": DATA[args.workload], "config": workload_config(args, wl),
@@ -566,6 +568,30 @@ def gpu_arm(args, wl, rank, world, local_rank):
                 others[name] = entry
         if rank == 0:
             line["workloads"] = others
+    # ---- the statistical build next to the exact one: what bit-exactness costs ------------------
+    fast_dir = os.path.join(ROOT, "volumetric-path-tracer_b200", "fast")
+    if rank == 0 and world == 1 and not args.no_fast and "VPT_LIB_DIR" not in os.environ \
+            and os.path.exists(os.path.join(fast_dir, "libvpt_cuda.so")):
+        # a process holds one build of the libraries: the fast one runs in a child
+        cmd = [sys.executable, os.path.abspath(__file__), "--workload", args.workload, "--steps",
+               str(min(args.steps, 6)), "--warmup", "3", "--pipeline", args.pipeline, "--no-workloads",
+               "--no-strong", "--no-cpu-baseline", "--no-fast"]
+        out = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, VPT_LIB_DIR=fast_dir))
+        try:
+            f = json.loads(out.stdout.strip().splitlines()[-1])
+            fr = f["roofline"]
+            line["fast"] = {"build": "-DVPT_FAST: FMA contraction, approximate division / square root, "
+                                     "CUDA libm, 1-FFMA slab tests; statistical parity only "
+                                     "(tests/test_gpu_fast.py)",
+                            "value": f["value"], "e2e": f["e2e"]["value"], "ms_per_step": f["ms_per_step"],
+                            "steps": f["steps"], "exact_over_fast": line["value"] / f["value"]}
+            line["roofline"]["exact"] = {"frac": line["roofline"]["frac"],
+                                         "whole_step_frac": line["roofline"]["whole_step"]["frac"]}
+            line["roofline"]["fast"] = {"frac": fr["frac"], "achieved": fr["achieved"],
+                                        "whole_step_frac": fr["whole_step"]["frac"],
+                                        "per_launch": fr["per_launch"]}
+        except Exception as ex:  # the headline must not depend on the side run
+            line["fast"] = {"unavailable": f"{type(ex).__name__}: {out.stderr[-300:]}"}
     # ---- strong scaling: BASELINE.json's split configurations --------------------------------
     if not args.no_strong:
         strong = {}
@@ -594,6 +620,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="skip the short runs of the other scenes")
     ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling leg")
+    ap.add_argument("--no-fast", action="store_true", help="skip the run of the statistical build")
     ap.add_argument("--side-steps", type=int, default=3)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)

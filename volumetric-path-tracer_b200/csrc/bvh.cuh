@@ -274,11 +274,19 @@ struct trav_t {
     auto rf = ld4(p + 6);
     auto ow = (unsigned)ld1(reinterpret_cast<const int*>(p + 7) + (oct >> 1)) >> ((oct & 1) * 16);
     unsigned m = 0;
+#if defined(VPT_FAST)
+    // statistical build: (b - o) * dinv as one FFMA per slab term, b * dinv + (-o * dinv)
+    float ox = -o.x * dinv.x, oy = -o.y * dinv.y, oz = -o.z * dinv.z;
+#define VPT_SLAB(b, d, od) fmaf(b, d, od)
+#else
+    const float ox = o.x, oy = o.y, oz = o.z;
+#define VPT_SLAB(b, d, od) ((b - od) * d)
+#endif
 #define VPT_WIDE_SLOT(k, c)                                                                     \
-  float lo##k = fmax2(fmax2(fmax2((nx.c - o.x) * dinv.x, (ny.c - o.y) * dinv.y),               \
-                          (nz.c - o.z) * dinv.z), tmin);                                      \
-  float hi##k = fmin2(fmin2(fmin2((fx.c - o.x) * dinv.x, (fy.c - o.y) * dinv.y),               \
-                          (fz.c - o.z) * dinv.z), tmax) * box_slack;                          \
+  float lo##k = fmax2(fmax2(fmax2(VPT_SLAB(nx.c, dinv.x, ox), VPT_SLAB(ny.c, dinv.y, oy)),     \
+                          VPT_SLAB(nz.c, dinv.z, oz)), tmin);                                 \
+  float hi##k = fmin2(fmin2(fmin2(VPT_SLAB(fx.c, dinv.x, ox), VPT_SLAB(fy.c, dinv.y, oy)),     \
+                          VPT_SLAB(fz.c, dinv.z, oz)), tmax) * box_slack;                     \
   int      r##k = f2i(rf.c);                                                                    \
   unsigned h##k = (ow >> (4 * k)) & 15u;                                                        \
   bool     p##k = lo##k <= hi##k && r##k != make_ref(0, ref_empty);                             \
@@ -288,6 +296,7 @@ struct trav_t {
     VPT_WIDE_SLOT(2, z)
     VPT_WIDE_SLOT(3, w)
 #undef VPT_WIDE_SLOT
+#undef VPT_SLAB
     VPT_WORK(wide_slot_tests, 4);
     // the first-visited slot (rank 0) goes on top: position = passing slots of higher rank
     if (p0) st.push(cur + popc4(m & (0u - (h0 << 1))), r0, lo0);
