@@ -243,6 +243,24 @@ int  vpt_cuda_upload_scene(const vpt_scene_desc* desc, vpt_scene** out);
  * `stats` may be null. */
 int  vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** out,
                                          vpt_lights_stats* stats);
+/* Shape BVH built on the device: an OPTIONAL replacement of make_bvh(shape)
+ * (yocto_bvh.cpp:526-571 -> build_bvh :447-507, split_middle :411-443). LBVH: primitive boxes and
+ * 30-bit Morton codes of their centroids, cub radix sort, Karras' hierarchy, boxes bottom-up, subtrees
+ * of <= 4 primitives folded into leaves (bvh_max_prims, :444). The tree comes back in the
+ * reference's own node format (children adjacent at start / start + 1) with its primitive order,
+ * sized nodes[<= 2 n + 1], primitives[n], and goes into vpt_bvh_desc like a host-built one.
+ * It is NOT the reference's tree: closest distances agree, but of two primitives at exactly the
+ * same distance another one may be reported (the reference keeps the later-tested one), so the
+ * bit-exact image gates hold only with the host builder; the first-hit gate records the ties. */
+typedef struct vpt_bvh_build_stats {
+  int32_t primitives, nodes;
+  float   keys_ms;       /* boxes, centroid bounds, Morton keys */
+  float   sort_ms;       /* cub::DeviceRadixSort, 64-bit keys */
+  float   hierarchy_ms;  /* hierarchy, box fit, leaf folding, renumbering */
+} vpt_bvh_build_stats;
+int  vpt_cuda_build_shape_bvh(const vpt_shape_desc* shape, vpt_bvh_node* nodes, size_t node_capacity,
+         int32_t* primitives, size_t prim_capacity, int32_t* num_nodes,
+         vpt_bvh_build_stats* stats);
 /* light `light` of an uploaded scene: ids = {instance, environment, sdf}; *num_elements floats of
  * CDF are copied to `cdf` if it is non-null and `capacity` suffices */
 int  vpt_cuda_scene_num_lights(const vpt_scene* scene);

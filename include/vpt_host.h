@@ -37,6 +37,8 @@ int  vpth_light_info(const vpth_scene* scene, int light, int32_t ids[3], int32_t
 int  vpth_light_cdf(const vpth_scene* scene, int light, float* cdf);
 /* make_lights on the device (vpt_cuda_upload_scene_device_lights): (re)uploads the scene with the
  * light list and CDFs built in HBM; renders created afterwards use it */
+/* rebuild the shape BVHs on the device (vpt_cuda_build_shape_bvh); `total` sums the per-shape stats */
+int  vpth_scene_use_device_bvh(vpth_scene* scene, vpt_bvh_build_stats* total);
 int  vpth_scene_use_device_lights(vpth_scene* scene, vpt_lights_stats* stats);
 /* light `light` as it lies on the device (light < 0: *num_elements = number of lights) */
 int  vpth_device_light(vpth_scene* scene, int light, int32_t ids[3], float* cdf, size_t capacity,

@@ -160,7 +160,7 @@ int main(int argc, const char** argv) {
            "  [--resolution 1..4096] [--shader NAME] [--samples 1..4096] [--bounces 1..128]\n"
            "  [--noparallel] [--noimplicitmis] [--stmaxiter 1..512]\n"
            "  [--pipeline auto|mega|wavefront] [--batch N] [--device K] [--device-lights]\n"
-           "  [--gpus N] [--exposure E] [--filmic] [--pratio P] [--display IMG.ppm|png]\n"
+           "  [--device-bvh] [--gpus N] [--exposure E] [--filmic] [--pratio P] [--display IMG.ppm|png]\n"
            "  [--display-every N]\n  shaders:");
     for (auto& n : pathtrace_shader_names) printf(" %s", n.c_str());
     printf("\n");
@@ -188,6 +188,7 @@ int main(int argc, const char** argv) {
     else if (a == "--batch") params.batch = ranged("batch", next(), 1, 4096);
     else if (a == "--device") device = std::stoi(next());
     else if (a == "--device-lights") device_lights = true;
+    else if (a == "--device-bvh") params.device_bvh = true;
     else if (a == "--gpus") params.gpus = ranged("gpus", next(), 1, 64);
     else if (a == "--exposure") params.exposure = std::stof(next());
     else if (a == "--filmic") params.filmic = true;

@@ -48,6 +48,11 @@ class TraceStats(C.Structure):
                 ("top_kernel_units", C.c_uint64), ("graph_launches", C.c_uint64)]
 
 
+class BvhBuildStats(C.Structure):
+    _fields_ = [("primitives", C.c_int32), ("nodes", C.c_int32), ("keys_ms", C.c_float),
+                ("sort_ms", C.c_float), ("hierarchy_ms", C.c_float)]
+
+
 class LightsStats(C.Structure):
     _fields_ = [("num_lights", C.c_int32), ("cdf_elements", C.c_uint64),
                 ("weights_ms", C.c_float), ("scan_ms", C.c_float)]
@@ -186,6 +191,12 @@ class Scene:
                 _check(self._host.vpth_device_light(self._h, i, ids, _fptr(cdf), C.c_size_t(cdf.size), C.byref(m)))
             out.append({"instance": ids[0], "environment": ids[1], "sdf": ids[2], "cdf": cdf})
         return out
+
+    def use_device_bvh(self) -> BvhBuildStats:
+        """Rebuild the shape BVHs on the device (LBVH, vpt_cuda_build_shape_bvh)."""
+        st = BvhBuildStats()
+        _check(self._host.vpth_scene_use_device_bvh(self._h, C.byref(st)))
+        return st
 
     def intersect(self, rays: np.ndarray, instance: int = -1):
         """rays: [n, 8] float32 -> (ids [n,3] int32: hit, instance, element; uvd [n,3])."""

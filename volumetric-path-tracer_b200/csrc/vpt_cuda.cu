@@ -20,6 +20,7 @@
 #include "tiling.cuh"
 #include "upload.cuh"
 #include "wavefront.cuh"
+#include "bvh_build.cuh"
 
 using namespace vpt;
 
@@ -454,6 +455,154 @@ int vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** 
   }
   if (stats) *stats = {(int32_t)lights.size(), total, w_ms, s_ms};
   return VPT_OK;
+}
+
+// ---- shape BVH on the device (bvh_build.cuh) ------------------------------------
+int vpt_cuda_build_shape_bvh(const vpt_shape_desc* shape, vpt_bvh_node* nodes, size_t node_capacity,
+    int32_t* primitives, size_t prim_capacity, int32_t* num_nodes, vpt_bvh_build_stats* stats) {
+  if (!shape || !nodes || !primitives || !num_nodes) return set_error(VPT_ERR_INVALID, "null argument");
+  if (auto r = require_device()) return r;
+  if (shape->num_points > 0 || shape->num_lines > 0)
+    return set_error(VPT_ERR_UNSUPPORTED, "point / line primitives");
+  // same precedence as the reference: triangles, then quads (yocto_bvh.cpp:532-560)
+  int  verts = shape->num_triangles > 0 ? 3 : 4;
+  int  n     = shape->num_triangles > 0 ? shape->num_triangles : shape->num_quads;
+  auto elems = shape->num_triangles > 0 ? shape->triangles : shape->quads;
+  *num_nodes = 0;
+  if (n <= 0) return VPT_OK;
+  if (!shape->positions || !elems) return set_error(VPT_ERR_INVALID, "null geometry");
+  if (prim_capacity < (size_t)n || node_capacity < 1)
+    return set_error(VPT_ERR_INVALID, "output buffers too small");
+  for (size_t k = 0; k < (size_t)n * verts; k++)
+    if (elems[k] < 0 || elems[k] >= shape->num_positions)
+      return set_error(VPT_ERR_INVALID, "vertex index out of range");
+  // one arena: positions | elems | boxes | centroids | keys x2 | ids x2 | children | ranges |
+  // parents x2 | axis | node boxes | leaf boxes | arrived | alive | rank | out nodes | bounds
+  struct arena_t {
+    char*  base = nullptr;
+    size_t used = 0;
+    void*  take(size_t bytes) {
+      used = (used + 255) / 256 * 256;
+      auto p = base ? base + used : nullptr;
+      used += bytes;
+      return p;
+    }
+  } arena;
+  size_t sort_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (unsigned long long*)nullptr,
+      (unsigned long long*)nullptr, (int*)nullptr, (int*)nullptr, n);
+  size_t scan_bytes = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (int*)nullptr, (int*)nullptr, n);
+  float *d_pos, *d_cent;
+  int *  d_elems, *d_ids, *d_sorted, *d_pint, *d_pleaf, *d_arrived, *d_alive, *d_rank;
+  unsigned long long *d_keys, *d_keys2;
+  int2 *   d_children, *d_ranges;
+  lbvh_box *d_boxes, *d_nboxes, *d_lboxes;
+  signed char*  d_axis;
+  vpt_bvh_node* d_out;
+  unsigned*     d_bounds;
+  void *        d_sort, *d_scan;
+  auto layout = [&]() {
+    arena.used = 0;
+    d_pos      = (float*)arena.take(sizeof(float) * 3 * (size_t)shape->num_positions);
+    d_elems    = (int*)arena.take(sizeof(int) * (size_t)n * verts);
+    d_boxes    = (lbvh_box*)arena.take(sizeof(lbvh_box) * (size_t)n);
+    d_cent     = (float*)arena.take(sizeof(float) * 3 * (size_t)n);
+    d_keys     = (unsigned long long*)arena.take(8 * (size_t)n);
+    d_keys2    = (unsigned long long*)arena.take(8 * (size_t)n);
+    d_ids      = (int*)arena.take(4 * (size_t)n);
+    d_sorted   = (int*)arena.take(4 * (size_t)n);
+    d_children = (int2*)arena.take(8 * (size_t)n);
+    d_ranges   = (int2*)arena.take(8 * (size_t)n);
+    d_pint     = (int*)arena.take(4 * (size_t)n);
+    d_pleaf    = (int*)arena.take(4 * (size_t)n);
+    d_axis     = (signed char*)arena.take((size_t)n);
+    d_nboxes   = (lbvh_box*)arena.take(sizeof(lbvh_box) * (size_t)n);
+    d_lboxes   = (lbvh_box*)arena.take(sizeof(lbvh_box) * (size_t)n);
+    d_arrived  = (int*)arena.take(4 * (size_t)n);
+    d_alive    = (int*)arena.take(4 * (size_t)n);
+    d_rank     = (int*)arena.take(4 * (size_t)n);
+    d_out      = (vpt_bvh_node*)arena.take(sizeof(vpt_bvh_node) * (2 * (size_t)n + 1));
+    d_bounds   = (unsigned*)arena.take(6 * sizeof(unsigned));
+    d_sort     = arena.take(sort_bytes);
+    d_scan     = arena.take(scan_bytes);
+  };
+  layout();
+  size_t total = arena.used + 256;
+  VPT_CUDA_TRY(cudaMalloc(&arena.base, total));
+  layout();
+  cudaEvent_t ev[4];
+  for (auto& e : ev) cudaEventCreate(&e);
+  auto done = [&](int code) {
+    for (auto& e : ev) cudaEventDestroy(e);
+    cudaFree(arena.base);
+    return code;
+  };
+#define VPT_LBVH_TRY(call)                                  \
+  do {                                                      \
+    cudaError_t e_ = (call);                                \
+    if (e_ != cudaSuccess) return done(cuda_fail(e_, #call)); \
+  } while (0)
+  int grid = (n + lbvh_block - 1) / lbvh_block;
+  VPT_LBVH_TRY(cudaMemcpy(d_pos, shape->positions, sizeof(float) * 3 * (size_t)shape->num_positions,
+      cudaMemcpyHostToDevice));
+  VPT_LBVH_TRY(cudaMemcpy(d_elems, elems, sizeof(int) * (size_t)n * verts, cudaMemcpyHostToDevice));
+  unsigned init_bounds[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0, 0, 0};
+  VPT_LBVH_TRY(cudaMemcpy(d_bounds, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice));
+  VPT_LBVH_TRY(cudaMemset(d_arrived, 0, 4 * (size_t)n));
+  VPT_LBVH_TRY(cudaMemset(d_pint, 0xff, 4 * (size_t)n));
+  VPT_LBVH_TRY(cudaMemset(d_pleaf, 0xff, 4 * (size_t)n));
+  cudaEventRecord(ev[0]);
+  k_lbvh_boxes<<<grid, lbvh_block>>>(d_pos, d_elems, verts, n, d_boxes, d_cent, d_bounds);
+  k_lbvh_keys<<<grid, lbvh_block>>>(d_cent, d_bounds, n, d_keys, d_ids);
+  cudaEventRecord(ev[1]);
+  VPT_LBVH_TRY(cub::DeviceRadixSort::SortPairs(d_sort, sort_bytes, d_keys, d_keys2, d_ids, d_sorted, n));
+  cudaEventRecord(ev[2]);
+  int alive_total = 0;
+  if (n > 1) {
+    k_lbvh_hierarchy<<<grid, lbvh_block>>>(d_keys2, n, d_children, d_ranges, d_pint, d_pleaf, d_axis);
+    k_lbvh_fit<<<grid, lbvh_block>>>(d_boxes, d_sorted, n, d_children, d_pint, d_pleaf, d_nboxes,
+        d_lboxes, d_arrived);
+    k_lbvh_alive<<<grid, lbvh_block>>>(d_ranges, n, d_alive);
+    VPT_LBVH_TRY(cub::DeviceScan::ExclusiveSum(d_scan, scan_bytes, d_alive, d_rank, n - 1));
+    k_lbvh_emit<<<grid, lbvh_block>>>(d_children, d_ranges, d_axis, d_alive, d_rank, d_nboxes,
+        d_lboxes, n, d_out);
+    int last[2] = {0, 0};
+    VPT_LBVH_TRY(cudaMemcpy(&last[0], d_rank + (n - 2), 4, cudaMemcpyDeviceToHost));
+    VPT_LBVH_TRY(cudaMemcpy(&last[1], d_alive + (n - 2), 4, cudaMemcpyDeviceToHost));
+    alive_total = last[0] + last[1];
+  }
+  cudaEventRecord(ev[3]);
+  VPT_LBVH_TRY(cudaEventSynchronize(ev[3]));
+  VPT_LBVH_TRY(cudaGetLastError());
+  VPT_LBVH_TRY(cudaMemcpy(primitives, d_sorted, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+  int count = 1 + 2 * alive_total;
+  if ((size_t)count > node_capacity) return done(set_error(VPT_ERR_INVALID, "node buffer too small"));
+  if (alive_total == 0) {
+    // <= 4 primitives: one leaf over all of them (its box is the union of the primitive boxes)
+    auto boxes = std::vector<lbvh_box>(n);
+    VPT_LBVH_TRY(cudaMemcpy(boxes.data(), d_boxes, sizeof(lbvh_box) * (size_t)n, cudaMemcpyDeviceToHost));
+    vpt_bvh_node root{};
+    for (int k = 0; k < 3; k++) root.bbox_min[k] = flt_max, root.bbox_max[k] = -flt_max;
+    for (auto& b : boxes)
+      for (int k = 0; k < 3; k++) {
+        root.bbox_min[k] = b.lo[k] < root.bbox_min[k] ? b.lo[k] : root.bbox_min[k];
+        root.bbox_max[k] = b.hi[k] > root.bbox_max[k] ? b.hi[k] : root.bbox_max[k];
+      }
+    root.start = 0, root.num = (int16_t)n, root.axis = 0, root.internal = 0;
+    nodes[0] = root;
+  } else {
+    VPT_LBVH_TRY(cudaMemcpy(nodes, d_out, sizeof(vpt_bvh_node) * (size_t)count, cudaMemcpyDeviceToHost));
+  }
+#undef VPT_LBVH_TRY
+  *num_nodes = count;
+  if (stats) {
+    stats->primitives = n, stats->nodes = count;
+    cudaEventElapsedTime(&stats->keys_ms, ev[0], ev[1]);
+    cudaEventElapsedTime(&stats->sort_ms, ev[1], ev[2]);
+    cudaEventElapsedTime(&stats->hierarchy_ms, ev[2], ev[3]);
+  }
+  return done(VPT_OK);
 }
 
 int vpt_cuda_scene_num_lights(const vpt_scene* scene) { return scene ? scene->flat.d.num_lights : 0; }

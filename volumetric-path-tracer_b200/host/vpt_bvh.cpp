@@ -121,9 +121,34 @@ bvh_shape make_bvh(const shape_data& shape) {
   return bvh;
 }
 
+// make_bvh(shape) on the device: LBVH in the reference's node format (vpt_cuda_build_shape_bvh)
+bvh_shape make_bvh_device(const shape_data& shape, vpt_bvh_build_stats* stats) {
+  auto desc = vpt_shape_desc{};
+  desc.positions = (const float*)shape.positions.data(), desc.num_positions = (int)shape.positions.size();
+  desc.triangles = (const int*)shape.triangles.data(), desc.num_triangles = (int)shape.triangles.size();
+  desc.quads = (const int*)shape.quads.data(), desc.num_quads = (int)shape.quads.size();
+  desc.num_points = (int)shape.points.size(), desc.num_lines = (int)shape.lines.size() / 2;
+  auto n   = desc.num_triangles > 0 ? desc.num_triangles : desc.num_quads;
+  auto bvh = bvh_data{};
+  if (stats) *stats = vpt_bvh_build_stats{};
+  if (n <= 0) return bvh;
+  bvh.nodes.resize(2 * (size_t)n + 1);
+  bvh.primitives.resize(n);
+  int count = 0;
+  if (vpt_cuda_build_shape_bvh(&desc, bvh.nodes.data(), bvh.nodes.size(), bvh.primitives.data(),
+          bvh.primitives.size(), &count, stats) != VPT_OK)
+    throw std::runtime_error(std::string("vpt_cuda_build_shape_bvh: ") + vpt_cuda_last_error());
+  bvh.nodes.resize(count);
+  return bvh;
+}
+
 bvh_scene make_bvh(const scene_data& scene, const pathtrace_params& params) {
   auto bvh = bvh_data{};
   bvh.shapes.resize(scene.shapes.size());
+  if (params.device_bvh) {
+    for (size_t idx = 0; idx < scene.shapes.size(); idx++)
+      bvh.shapes[idx] = make_bvh_device(scene.shapes[idx]);
+  } else {
   // one shape per task, like the reference's parallel_for over shapes
   auto nthreads = params.noparallel ? 1u : std::max(1u, std::thread::hardware_concurrency());
   nthreads      = (unsigned)std::min<size_t>(nthreads, std::max<size_t>(1, scene.shapes.size()));
@@ -144,6 +169,7 @@ bvh_scene make_bvh(const scene_data& scene, const pathtrace_params& params) {
     for (auto& t : threads) t.join();
   }
   if (!error.empty()) throw std::runtime_error(error);
+  }
 
   auto bboxes = std::vector<bbox3f>(scene.instances.size());
   for (size_t idx = 0; idx < bboxes.size(); idx++) {

@@ -149,6 +149,25 @@ int vpth_light_cdf(const vpth_scene* s, int light, float* cdf) {
   return VPT_OK;
 }
 
+int vpth_scene_use_device_bvh(vpth_scene* s, vpt_bvh_build_stats* total) {
+  if (!s) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto params       = pathtrace_params{};
+    params.device_bvh = true;
+    auto sum          = vpt_bvh_build_stats{};
+    // shape by shape for the statistics, then the (host) scene level over the new root boxes
+    for (auto& shape : s->scene.shapes) {
+      auto st = vpt_bvh_build_stats{};
+      make_bvh_device(shape, &st);
+      sum.primitives += st.primitives, sum.nodes += st.nodes, sum.keys_ms += st.keys_ms;
+      sum.sort_ms += st.sort_ms, sum.hierarchy_ms += st.hierarchy_ms;
+    }
+    s->bvh    = make_bvh(s->scene, params);
+    s->device = nullptr;  // uploaded again on next use
+    if (total) *total = sum;
+  });
+}
+
 int vpth_scene_use_device_lights(vpth_scene* s, vpt_lights_stats* stats) {
   if (!s) return VPT_ERR_INVALID;
   return guarded([&] { s->device = upload_scene_device_lights(s->scene, s->bvh, stats); });

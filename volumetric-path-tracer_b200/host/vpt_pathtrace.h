@@ -67,6 +67,10 @@ struct pathtrace_params {
   // pixel's PCG32 stream from r << 40 draws ahead; get_render sums the images on the first GPU
   // (P2P over NVLink, vpt_cuda_state_add_peer). 1 GPU = the reference's streams exactly.
   int                   gpus                = 1;
+  // make_bvh builds the shape BVHs on the device (LBVH) instead of the
+  // reference's middle-split trees: same closest hits, exact-distance ties may pick another
+  // primitive, so the bit-exact image gates need the default (false)
+  bool                  device_bvh          = false;
 };
 
 // Samples GPU `rank` of `gpus` takes out of a call of `batch` samples: contiguous ranges, the
@@ -107,6 +111,7 @@ pathtrace_state make_state(const scene_data& scene, const pathtrace_params& para
 // yocto_pathtrace.cpp:955, yocto_bvh.cpp:411-611).
 bvh_scene make_bvh(const scene_data& scene, const pathtrace_params& params);
 bvh_shape make_bvh(const shape_data& shape);
+bvh_shape make_bvh_device(const shape_data& shape, vpt_bvh_build_stats* stats = nullptr);
 
 // Light list and sampling CDFs (yocto_pathtrace.cpp:983-1049).
 pathtrace_lights make_lights(const scene_data& scene, const pathtrace_params& params);
