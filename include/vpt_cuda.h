@@ -261,6 +261,26 @@ typedef struct vpt_bvh_build_stats {
 int  vpt_cuda_build_shape_bvh(const vpt_shape_desc* shape, vpt_bvh_node* nodes, size_t node_capacity,
          int32_t* primitives, size_t prim_capacity, int32_t* num_nodes,
          vpt_bvh_build_stats* stats);
+/* Subdivision surfaces on the device: the three numeric stages of
+ * tesselate_surface (yocto_pathtrace.cpp:1230-1273). Results equal the reference's bit for bit.
+ *
+ * vpt_cuda_catmullclark: `levels` rounds of tesselate_catmullclark (:1119-1228) on a quad mesh
+ *   (a triangle is a quad with z == w). dim = 3 with lock_boundary = 0 for positions, dim = 2
+ *   with lock_boundary = 1 for texture coordinates, as tesselate_surface calls it. Outputs are
+ *   malloc'ed by the library (quads [n][4], verts [n][dim]); release with vpt_cuda_free_host.
+ * vpt_cuda_vertex_normals: quads_normals (verts_per = 4) / triangles_normals (verts_per = 3)
+ *   (yocto_shape.cpp:1478-1510): area-weighted face normals summed per vertex in face order.
+ * vpt_cuda_displace: positions[i] += normals[i] * displacement * d(texcoords[i]) with d = mean
+ *   of the displacement texture's rgb (bilinear, sRGB decoded), minus 0.5 for 8-bit textures
+ *   (:1256-1263). `positions` is updated in place. */
+int  vpt_cuda_catmullclark(const int32_t* quads, int nquads, const float* verts, int nverts, int dim,
+         int lock_boundary, int levels, int32_t** out_quads, int32_t* out_nquads,
+         float** out_verts, int32_t* out_nverts);
+void vpt_cuda_free_host(void* p);
+int  vpt_cuda_vertex_normals(const int32_t* elems, int nelems, int verts_per, const float* positions,
+         int nverts, float* normals);
+int  vpt_cuda_displace(float* positions, const float* normals, const float* texcoords, int nverts,
+         const vpt_texture_desc* texture, float displacement);
 /* light `light` of an uploaded scene: ids = {instance, environment, sdf}; *num_elements floats of
  * CDF are copied to `cdf` if it is non-null and `capacity` suffices */
 int  vpt_cuda_scene_num_lights(const vpt_scene* scene);

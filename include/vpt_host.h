@@ -37,6 +37,14 @@ int  vpth_light_info(const vpth_scene* scene, int light, int32_t ids[3], int32_t
 int  vpth_light_cdf(const vpth_scene* scene, int light, float* cdf);
 /* make_lights on the device (vpt_cuda_upload_scene_device_lights): (re)uploads the scene with the
  * light list and CDFs built in HBM; renders created afterwards use it */
+/* subdivision surfaces: read the control cages of an archive (tools/vpt_export --dump-subdivs /
+ * --keep-subdivs), run tesselate_surfaces with the numeric stages on the device, read a shape back */
+int  vpth_scene_load_subdivs(vpth_scene* scene, const char* path);
+int  vpth_scene_tesselate(vpth_scene* scene);
+int  vpth_shape_sizes(const vpth_scene* scene, int shape, int32_t sizes[6]); /* positions, normals,
+                                                         texcoords, triangles, quads, colors */
+int  vpth_shape_copy(const vpth_scene* scene, int shape, float* positions, float* normals,
+         float* texcoords, int32_t* triangles, int32_t* quads); /* null: skip */
 /* rebuild the shape BVHs on the device (vpt_cuda_build_shape_bvh); `total` sums the per-shape stats */
 int  vpth_scene_use_device_bvh(vpth_scene* scene, vpt_bvh_build_stats* total);
 int  vpth_scene_use_device_lights(vpth_scene* scene, vpt_lights_stats* stats);

@@ -37,12 +37,21 @@ def link_tree(src: str, dst: str) -> None:
                 os.symlink(os.path.join(base, f), target)
 
 
-def export(scene_dir: str, json_name: str, out_name: str, force: bool = False) -> str:
+def export(scene_dir: str, json_name: str, out_name: str, force: bool = False,
+           keep_subdivs: bool = False) -> str:
+    """Reference loaders (+ reference tessellation unless keep_subdivs) -> archive. The control
+    cages of the scene's subdivision surfaces also go to <out_name>.subdivs.vptarch, a small file
+    from which tests re-tessellate on the device and compare with the reference's result."""
     out = os.path.join(BUILT, out_name + ".vptscene")
     if os.path.exists(out) and not force:
         return out
     os.makedirs(BUILT, exist_ok=True)
-    subprocess.run([EXPORT, os.path.join(scene_dir, json_name), out + ".tmp"], check=True)
+    cmd = [EXPORT, os.path.join(scene_dir, json_name), out + ".tmp"]
+    if keep_subdivs:
+        cmd.append("--keep-subdivs")
+    else:
+        cmd += ["--dump-subdivs", os.path.join(BUILT, out_name + ".subdivs.vptarch")]
+    subprocess.run(cmd, check=True)
     os.replace(out + ".tmp", out)
     return out
 

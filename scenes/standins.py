@@ -340,6 +340,8 @@ def build_02_rollingteapot(force=False):
         cage = os.path.join(d, sub, "rollingteapot-subdiv.obj")
         if not os.path.exists(cage):
             write_obj_lathe(cage, TEAPOT_PROFILE, 24, handle=((0.088, 0.06, 0.0), 0.028, 0.007, 8))
+    # the same scene with its subdivision surface left to the device tessellation
+    export(d, "rollingteapot.json", "02_rollingteapot_subdiv", force, keep_subdivs=True)
     return export(d, "rollingteapot.json", "02_rollingteapot", force)
 
 

@@ -9,7 +9,11 @@
 // library and the oracle renderer (ref_render) can read. Compiled against the
 // reference headers where they lie; exists only where /root/reference does.
 //
-// usage: vpt_export <scene.json> <out.vptscene>
+// usage: vpt_export <scene.json> <out.vptscene> [--keep-subdivs] [--dump-subdivs <file>]
+//   --keep-subdivs        leave subdivision surfaces un-tessellated: the archive carries the
+//                         control cages (subdiv<i>.*) and ypathtrace tessellates them on the GPU
+//   --dump-subdivs FILE   additionally write only the control cages (tests compare the device
+//                         tessellation of FILE with the reference-tessellated archive)
 #include <yocto/yocto_scene.h>
 #include <yocto/yocto_sceneio.h>
 #include <yocto/yocto_sdfs.h>
@@ -39,9 +43,45 @@ int main(int argc, const char** argv) {
     fprintf(stderr, "vpt_export: %s\n", error.c_str());
     return 1;
   }
-  tesselate_surfaces(scene);
+  auto keep_subdivs = false;
+  auto dump_subdivs = string{};
+  for (int i = 3; i < argc; i++) {
+    if (string{argv[i]} == "--keep-subdivs") keep_subdivs = true;
+    if (string{argv[i]} == "--dump-subdivs" && i + 1 < argc) dump_subdivs = argv[++i];
+  }
+  auto put_subdivs = [&](vpt::archive& to) {
+    int n = (int)scene.subdivs.size();
+    to.add_i32("subdivs.count", {1}, &n);
+    for (int i = 0; i < n; i++) {
+      auto& s   = scene.subdivs[i];
+      auto  pre = "subdiv" + std::to_string(i) + ".";
+      to.add_i32(pre + "quadspos", {s.quadspos.size(), 4}, (const int*)s.quadspos.data());
+      if (!s.quadsnorm.empty())
+        to.add_i32(pre + "quadsnorm", {s.quadsnorm.size(), 4}, (const int*)s.quadsnorm.data());
+      if (!s.quadstexcoord.empty())
+        to.add_i32(pre + "quadstexcoord", {s.quadstexcoord.size(), 4}, (const int*)s.quadstexcoord.data());
+      to.add_f32(pre + "positions", {s.positions.size(), 3}, (const float*)s.positions.data());
+      if (!s.normals.empty())
+        to.add_f32(pre + "normals", {s.normals.size(), 3}, (const float*)s.normals.data());
+      if (!s.texcoords.empty())
+        to.add_f32(pre + "texcoords", {s.texcoords.size(), 2}, (const float*)s.texcoords.data());
+      int params[5] = {s.subdivisions, s.catmullclark ? 1 : 0, s.smooth ? 1 : 0, s.displacement_tex, s.shape};
+      to.add_i32(pre + "params", {5}, params);
+      to.add_f32(pre + "displacement", {1}, &s.displacement);
+    }
+  };
+  if (!dump_subdivs.empty()) {
+    auto only = vpt::archive{};
+    put_subdivs(only);
+    if (!only.save(dump_subdivs, error)) {
+      fprintf(stderr, "vpt_export: %s\n", error.c_str());
+      return 1;
+    }
+  }
+  if (!keep_subdivs) tesselate_surfaces(scene);
 
   auto ar = vpt::archive{};
+  if (keep_subdivs) put_subdivs(ar);
   int  meta[4] = {1, 0, 0, 0};
   ar.add_i32("meta", {4}, meta);
 

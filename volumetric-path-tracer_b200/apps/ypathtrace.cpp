@@ -2,7 +2,7 @@
 //
 // Mirrors run() / run_offline() of the reference CLI
 // (apps/ypathtrace/ypathtrace.cpp:41-87, :307-341): same flags, defaults and
-// call sequence (load_scene [already tessellated, tools/vpt_export] -> make_bvh -> make_lights ->
+// call sequence (load_scene -> tesselate_surfaces -> make_bvh -> make_lights ->
 // make_state -> pathtrace_samples x N -> get_render -> save_image). Differences:
 // the scene is a ".vptscene" archive (asset loading stays with the reference's
 // loaders, see tools/vpt_export.cpp); --interactive is unavailable on
@@ -225,6 +225,12 @@ int main(int argc, const char** argv) {
     auto scene = scene_data{};
     if (!load_scene(scenename, scene, error)) print_fatal(error);
     printf("load scene: %.3f s\n", since(t0));
+    if (!scene.subdivs.empty()) {  // archives exported with --keep-subdivs
+      t0 = clock();
+      auto count = scene.subdivs.size();
+      tesselate_surfaces(scene);
+      printf("tesselate surfaces (device): %.3f s (%zu subdivs)\n", since(t0), count);
+    }
     t0       = clock();
     auto bvh = make_bvh(scene, params);
     printf("build bvh: %.3f s\n", since(t0));

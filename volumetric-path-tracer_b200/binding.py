@@ -192,6 +192,23 @@ class Scene:
             out.append({"instance": ids[0], "environment": ids[1], "sdf": ids[2], "cdf": cdf})
         return out
 
+    def load_subdivs(self, path: str) -> None:
+        _check(self._host.vpth_scene_load_subdivs(self._h, path.encode()))
+
+    def tesselate(self) -> None:
+        """tesselate_surfaces with Catmull-Clark / normals / displacement on the device."""
+        _check(self._host.vpth_scene_tesselate(self._h))
+
+    def shape(self, index: int) -> dict:
+        sizes = (C.c_int32 * 6)()
+        _check(self._host.vpth_shape_sizes(self._h, index, sizes))
+        out = {"positions": np.zeros((sizes[0], 3), np.float32), "normals": np.zeros((sizes[1], 3), np.float32),
+               "texcoords": np.zeros((sizes[2], 2), np.float32), "triangles": np.zeros((sizes[3], 3), np.int32),
+               "quads": np.zeros((sizes[4], 4), np.int32)}
+        _check(self._host.vpth_shape_copy(self._h, index, _fptr(out["positions"]), _fptr(out["normals"]),
+                                          _fptr(out["texcoords"]), _iptr(out["triangles"]), _iptr(out["quads"])))
+        return out
+
     def use_device_bvh(self) -> BvhBuildStats:
         """Rebuild the shape BVHs on the device (LBVH, vpt_cuda_build_shape_bvh)."""
         st = BvhBuildStats()

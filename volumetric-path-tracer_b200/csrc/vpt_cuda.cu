@@ -21,6 +21,7 @@
 #include "upload.cuh"
 #include "wavefront.cuh"
 #include "bvh_build.cuh"
+#include "tesselate.cuh"
 
 using namespace vpt;
 
@@ -603,6 +604,265 @@ int vpt_cuda_build_shape_bvh(const vpt_shape_desc* shape, vpt_bvh_node* nodes, s
     cudaEventElapsedTime(&stats->hierarchy_ms, ev[2], ev[3]);
   }
   return done(VPT_OK);
+}
+
+// ---- Catmull-Clark subdivision, vertex normals, displacement (tesselate.cuh) ----
+}  // extern "C"
+namespace {
+template <typename T>
+struct dev_buf {  // scene-preparation code: plain cudaMalloc'ed scratch, freed on scope exit
+  T*     p = nullptr;
+  size_t n = 0;
+  dev_buf() = default;
+  explicit dev_buf(size_t count) { alloc(count); }
+  dev_buf(const dev_buf&) = delete;
+  dev_buf& operator=(const dev_buf&) = delete;
+  cudaError_t alloc(size_t count) {
+    release();
+    n = count;
+    return cudaMalloc(&p, sizeof(T) * (count ? count : 1));
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+  }
+  void swap(dev_buf& o) { std::swap(p, o.p), std::swap(n, o.n); }
+  ~dev_buf() { release(); }
+};
+inline int tess_grid(size_t n) { return (int)((n + tess_block - 1) / tess_block); }
+
+template <typename K, typename V>
+cudaError_t sort_pairs(const K* kin, K* kout, const V* vin, V* vout, int n, int end_bit) {
+  size_t bytes = 0;
+  auto   e = cub::DeviceRadixSort::SortPairs(nullptr, bytes, kin, kout, vin, vout, n, 0, end_bit);
+  if (e != cudaSuccess) return e;
+  dev_buf<char> tmp;
+  e = tmp.alloc(bytes);
+  if (e != cudaSuccess) return e;
+  return cub::DeviceRadixSort::SortPairs(tmp.p, bytes, kin, kout, vin, vout, n, 0, end_bit);
+}
+cudaError_t exclusive_sum(const int* in, int* out, int n) {
+  size_t bytes = 0;
+  auto   e = cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, n);
+  if (e != cudaSuccess) return e;
+  dev_buf<char> tmp;
+  e = tmp.alloc(bytes);
+  if (e != cudaSuccess) return e;
+  return cub::DeviceScan::ExclusiveSum(tmp.p, bytes, in, out, n);
+}
+int bits_for(unsigned max_value) {
+  int b = 1;
+  while (b < 32 && (max_value >> b)) b++;
+  return b;
+}
+
+// one level of tesselate_catmullclark on device buffers: (quads, verts) -> (tquads, avert)
+template <int D>
+cudaError_t catmullclark_level(dev_buf<int4>& quads, dev_buf<float>& verts, int& nf, int& nv,
+    bool lock_boundary) {
+#define TRY(x)                       \
+  do {                               \
+    cudaError_t e_ = (x);            \
+    if (e_ != cudaSuccess) return e_; \
+  } while (0)
+  int ns = 4 * nf;
+  dev_buf<unsigned long long> keys, keys_sorted;
+  dev_buf<int> pos, pos_sorted, face_count, face_offset, head, run;
+  TRY(keys.alloc(ns));
+  TRY(keys_sorted.alloc(ns));
+  TRY(pos.alloc(ns));
+  TRY(pos_sorted.alloc(ns));
+  TRY(face_count.alloc(nf + 1));
+  TRY(face_offset.alloc(nf + 1));
+  TRY(head.alloc(ns + 1));
+  TRY(run.alloc(ns + 1));
+  TRY(cudaMemset(face_count.p, 0, sizeof(int) * (nf + 1)));
+  TRY(cudaMemset(head.p, 0, sizeof(int) * (ns + 1)));
+  k_tess_sides<<<tess_grid(ns), tess_block>>>(quads.p, nf, keys.p, pos.p, face_count.p);
+  TRY((sort_pairs(keys.p, keys_sorted.p, pos.p, pos_sorted.p, ns, 64)));
+  k_tess_heads<<<tess_grid(ns), tess_block>>>(keys_sorted.p, ns, head.p);
+  TRY(exclusive_sum(head.p, run.p, ns + 1));       // run[ns] = number of unique edges
+  TRY(exclusive_sum(face_count.p, face_offset.p, nf + 1));  // face_offset[nf] = new quads
+  int ne = 0, nq = 0;
+  TRY(cudaMemcpy(&ne, run.p + ns, sizeof(int), cudaMemcpyDeviceToHost));
+  TRY(cudaMemcpy(&nq, face_offset.p + nf, sizeof(int), cudaMemcpyDeviceToHost));
+  dev_buf<int> first_pos, uid, run_start, first_sorted, order, nfaces, index_of_unique, side_edge;
+  dev_buf<int2> edges;
+  TRY(first_pos.alloc(ne));
+  TRY(uid.alloc(ne));
+  TRY(run_start.alloc(ne));
+  TRY(first_sorted.alloc(ne));
+  TRY(order.alloc(ne));
+  TRY(nfaces.alloc(ne));
+  TRY(index_of_unique.alloc(ne));
+  TRY(side_edge.alloc(ns));
+  TRY(edges.alloc(ne));
+  k_tess_uniques<<<tess_grid(ns), tess_block>>>(keys_sorted.p, pos_sorted.p, head.p, run.p, ns,
+      first_pos.p, uid.p, run_start.p);
+  // edges numbered in the order the reference's insert_edge first meets them
+  TRY((sort_pairs((const unsigned*)first_pos.p, (unsigned*)first_sorted.p, uid.p, order.p, ne,
+      bits_for((unsigned)ns))));
+  k_tess_edges<<<tess_grid(ne), tess_block>>>(keys_sorted.p, order.p, run_start.p, ne, ns, edges.p,
+      nfaces.p, index_of_unique.p);
+  k_tess_side_edges<<<tess_grid(ns), tess_block>>>(keys_sorted.p, pos_sorted.p, head.p, run.p,
+      index_of_unique.p, ns, side_edge.p);
+  int ntv = nv + ne + nf;
+  dev_buf<float> tverts, avert;
+  dev_buf<int4>  tquads;
+  dev_buf<signed char> val;
+  dev_buf<int>   acount;
+  TRY(tverts.alloc((size_t)D * ntv));
+  TRY(avert.alloc((size_t)D * ntv));
+  TRY(tquads.alloc(nq));
+  TRY(val.alloc(ntv));
+  TRY(acount.alloc(ntv));
+  k_tess_vertices<D><<<tess_grid(ntv), tess_block>>>(verts.p, nv, edges.p, ne, quads.p, nf, tverts.p);
+  k_tess_faces<<<tess_grid(nf), tess_block>>>(quads.p, nf, side_edge.p, face_offset.p, nv, ne, tquads.p);
+  TRY(cudaMemset(val.p, 2, ntv));
+  TRY(cudaMemset(avert.p, 0, sizeof(float) * D * ntv));
+  TRY(cudaMemset(acount.p, 0, sizeof(int) * ntv));
+  k_tess_boundary<D><<<tess_grid(ne), tess_block>>>(edges.p, nfaces.p, ne, nv, lock_boundary ? 1 : 0,
+      tverts.p, val.p, avert.p, acount.p, 0);
+  k_tess_boundary<D><<<tess_grid(ne), tess_block>>>(edges.p, nfaces.p, ne, nv, lock_boundary ? 1 : 0,
+      tverts.p, val.p, avert.p, acount.p, 1);
+  int nentries = 4 * nq;
+  dev_buf<unsigned> vkey, vkey_sorted;
+  dev_buf<int>      entry, entry_sorted;
+  TRY(vkey.alloc(nentries));
+  TRY(vkey_sorted.alloc(nentries));
+  TRY(entry.alloc(nentries));
+  TRY(entry_sorted.alloc(nentries));
+  k_tess_corners<<<tess_grid(nentries), tess_block>>>(tquads.p, nq, vkey.p, entry.p);
+  TRY((sort_pairs(vkey.p, vkey_sorted.p, entry.p, entry_sorted.p, nentries, bits_for((unsigned)ntv))));
+  k_tess_average<D><<<tess_grid(ntv), tess_block>>>(tquads.p, vkey_sorted.p, entry_sorted.p, nentries,
+      tverts.p, ntv, val.p, avert.p, acount.p);
+  TRY(cudaGetLastError());
+  TRY(cudaDeviceSynchronize());
+  quads.swap(tquads), verts.swap(avert);
+  nf = nq, nv = ntv;
+  return cudaSuccess;
+#undef TRY
+}
+}  // namespace
+extern "C" {
+
+void vpt_cuda_free_host(void* p) { free(p); }
+
+int vpt_cuda_catmullclark(const int32_t* quads, int nquads, const float* verts, int nverts, int dim,
+    int lock_boundary, int levels, int32_t** out_quads, int32_t* out_nquads, float** out_verts,
+    int32_t* out_nverts) {
+  if (!out_quads || !out_nquads || !out_verts || !out_nverts || nquads < 0 || nverts < 0 ||
+      (dim != 2 && dim != 3) || levels < 0 || (nquads > 0 && !quads) || (nverts > 0 && !verts))
+    return set_error(VPT_ERR_INVALID, "bad argument");
+  *out_quads = nullptr, *out_verts = nullptr, *out_nquads = 0, *out_nverts = 0;
+  if (auto r = require_device()) return r;
+  for (size_t k = 0; k < (size_t)nquads * 4; k++)
+    if (quads[k] < 0 || quads[k] >= nverts) return set_error(VPT_ERR_INVALID, "vertex index out of range");
+  dev_buf<int4>  dq;
+  dev_buf<float> dv;
+  VPT_CUDA_TRY(dq.alloc(nquads));
+  VPT_CUDA_TRY(dv.alloc((size_t)dim * nverts));
+  VPT_CUDA_TRY(cudaMemcpy(dq.p, quads, sizeof(int4) * (size_t)nquads, cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(dv.p, verts, sizeof(float) * dim * (size_t)nverts, cudaMemcpyHostToDevice));
+  int nf = nquads, nv = nverts;
+  for (int level = 0; level < levels && nf > 0; level++) {
+    if ((long long)nf * 16 > 0x7fffffffLL) return set_error(VPT_ERR_UNSUPPORTED, "mesh too large");
+    auto e = dim == 3 ? catmullclark_level<3>(dq, dv, nf, nv, lock_boundary != 0)
+                      : catmullclark_level<2>(dq, dv, nf, nv, lock_boundary != 0);
+    if (e != cudaSuccess) return cuda_fail(e, "catmullclark level");
+  }
+  auto hq = (int32_t*)malloc(sizeof(int4) * (size_t)(nf ? nf : 1));
+  auto hv = (float*)malloc(sizeof(float) * dim * (size_t)(nv ? nv : 1));
+  if (!hq || !hv) {
+    free(hq), free(hv);
+    return set_error(VPT_ERR_OUT_OF_MEMORY, "host allocation failed");
+  }
+  auto e = cudaMemcpy(hq, dq.p, sizeof(int4) * (size_t)nf, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(hv, dv.p, sizeof(float) * dim * (size_t)nv, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    free(hq), free(hv);
+    return cuda_fail(e, "catmullclark download");
+  }
+  *out_quads = hq, *out_nquads = nf, *out_verts = hv, *out_nverts = nv;
+  return VPT_OK;
+}
+
+int vpt_cuda_vertex_normals(const int32_t* elems, int nelems, int verts_per, const float* positions,
+    int nverts, float* normals) {
+  if (!normals || nelems < 0 || nverts < 0 || (verts_per != 3 && verts_per != 4) ||
+      (nelems > 0 && !elems) || (nverts > 0 && !positions))
+    return set_error(VPT_ERR_INVALID, "bad argument");
+  if (auto r = require_device()) return r;
+  if (nverts == 0) return VPT_OK;
+  int n = verts_per * nelems;
+  for (int k = 0; k < n; k++)
+    if (elems[k] < 0 || elems[k] >= nverts) return set_error(VPT_ERR_INVALID, "vertex index out of range");
+  dev_buf<int> de, entry, entry_sorted;
+  dev_buf<unsigned> vkey, vkey_sorted;
+  dev_buf<float> dp, dn;
+  VPT_CUDA_TRY(de.alloc(n));
+  VPT_CUDA_TRY(entry.alloc(n));
+  VPT_CUDA_TRY(entry_sorted.alloc(n));
+  VPT_CUDA_TRY(vkey.alloc(n));
+  VPT_CUDA_TRY(vkey_sorted.alloc(n));
+  VPT_CUDA_TRY(dp.alloc(3 * (size_t)nverts));
+  VPT_CUDA_TRY(dn.alloc(3 * (size_t)nverts));
+  VPT_CUDA_TRY(cudaMemcpy(de.p, elems, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(dp.p, positions, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyHostToDevice));
+  if (n > 0) {
+    k_tess_elem_corners<<<tess_grid(n), tess_block>>>(de.p, nelems, verts_per, vkey.p, entry.p);
+    VPT_CUDA_TRY((sort_pairs(vkey.p, vkey_sorted.p, entry.p, entry_sorted.p, n, 32)));
+  }
+  k_tess_normals<<<tess_grid(nverts), tess_block>>>(de.p, verts_per, vkey_sorted.p, entry_sorted.p, n,
+      dp.p, nverts, dn.p);
+  VPT_CUDA_TRY(cudaGetLastError());
+  VPT_CUDA_TRY(cudaMemcpy(normals, dn.p, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyDeviceToHost));
+  return VPT_OK;
+}
+
+int vpt_cuda_displace(float* positions, const float* normals, const float* texcoords, int nverts,
+    const vpt_texture_desc* texture, float displacement) {
+  if (!positions || !normals || !texcoords || !texture || nverts < 0)
+    return set_error(VPT_ERR_INVALID, "bad argument");
+  if (auto r = require_device()) return r;
+  if (nverts == 0) return VPT_OK;
+  size_t texels = (size_t)texture->width * texture->height;
+  if (texture->width < 0 || texture->height < 0 || (texels > 0 && !texture->pixelsf && !texture->pixelsb))
+    return set_error(VPT_ERR_INVALID, "bad texture");
+  // a one-texture scene view: record 0, its texel pool, the host-built sRGB table
+  dev_buf<float> dp, dn, dt, lut;
+  dev_buf<f4>    texf;
+  dev_buf<unsigned char> texb;
+  dev_buf<i4>    rec;
+  VPT_CUDA_TRY(dp.alloc(3 * (size_t)nverts));
+  VPT_CUDA_TRY(dn.alloc(3 * (size_t)nverts));
+  VPT_CUDA_TRY(dt.alloc(2 * (size_t)nverts));
+  VPT_CUDA_TRY(lut.alloc(256));
+  VPT_CUDA_TRY(rec.alloc(1));
+  VPT_CUDA_TRY(texf.alloc(texture->pixelsf ? texels : 0));
+  VPT_CUDA_TRY(texb.alloc(texture->pixelsf ? 0 : 4 * texels));
+  float table[256];
+  for (int b = 0; b < 256; b++) {
+    float srgb = b / 255.0f;
+    table[b]   = ((double)srgb <= 0.04045) ? srgb / 12.92f : powf((srgb + 0.055f) / (1.0f + 0.055f), 2.4f);
+  }
+  i4 record = {texture->width, texture->height, (texture->linear ? 1 : 0) | (texture->pixelsf ? 2 : 0), 0};
+  VPT_CUDA_TRY(cudaMemcpy(rec.p, &record, sizeof(record), cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(lut.p, table, sizeof(table), cudaMemcpyHostToDevice));
+  if (texture->pixelsf)
+    VPT_CUDA_TRY(cudaMemcpy(texf.p, texture->pixelsf, sizeof(f4) * texels, cudaMemcpyHostToDevice));
+  else if (texels)
+    VPT_CUDA_TRY(cudaMemcpy(texb.p, texture->pixelsb, 4 * texels, cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(dp.p, positions, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(dn.p, normals, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyHostToDevice));
+  VPT_CUDA_TRY(cudaMemcpy(dt.p, texcoords, sizeof(float) * 2 * (size_t)nverts, cudaMemcpyHostToDevice));
+  DScene sc{};
+  sc.textures = rec.p, sc.texf = texf.p, sc.texb = texb.p, sc.srgb_lut = lut.p;
+  k_tess_displace<<<tess_grid(nverts), tess_block>>>(sc, texture->pixelsf ? 0 : 1, displacement, dn.p,
+      dt.p, nverts, dp.p);
+  VPT_CUDA_TRY(cudaGetLastError());
+  VPT_CUDA_TRY(cudaMemcpy(positions, dp.p, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyDeviceToHost));
+  return VPT_OK;
 }
 
 int vpt_cuda_scene_num_lights(const vpt_scene* scene) { return scene ? scene->flat.d.num_lights : 0; }

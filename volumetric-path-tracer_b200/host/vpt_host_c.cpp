@@ -149,6 +149,48 @@ int vpth_light_cdf(const vpth_scene* s, int light, float* cdf) {
   return VPT_OK;
 }
 
+int vpth_scene_load_subdivs(vpth_scene* s, const char* path) {
+  if (!s || !path) return VPT_ERR_INVALID;
+  return guarded([&] {
+    auto error = std::string{};
+    if (!load_subdivs(path, s->scene, error)) throw std::runtime_error(error);
+  });
+}
+
+// tesselate_surfaces on the device; the BVHs, lights and the device scene are rebuilt
+int vpth_scene_tesselate(vpth_scene* s) {
+  if (!s) return VPT_ERR_INVALID;
+  return guarded([&] {
+    for (auto& sd : s->scene.subdivs)  // nothing of an earlier tessellation may survive
+      if (sd.shape >= 0 && sd.shape < (int)s->scene.shapes.size()) s->scene.shapes[sd.shape] = shape_data{};
+    tesselate_surfaces(s->scene);
+    auto params = pathtrace_params{};
+    s->bvh      = make_bvh(s->scene, params);
+    s->lights   = make_lights(s->scene, params);
+    s->device   = nullptr;
+  });
+}
+
+int vpth_shape_sizes(const vpth_scene* s, int shape, int32_t sizes[6]) {
+  if (!s || !sizes || shape < 0 || shape >= (int)s->scene.shapes.size()) return VPT_ERR_INVALID;
+  auto& sh = s->scene.shapes[shape];
+  sizes[0] = (int)sh.positions.size(), sizes[1] = (int)sh.normals.size(), sizes[2] = (int)sh.texcoords.size();
+  sizes[3] = (int)sh.triangles.size(), sizes[4] = (int)sh.quads.size(), sizes[5] = (int)sh.colors.size();
+  return VPT_OK;
+}
+
+int vpth_shape_copy(const vpth_scene* s, int shape, float* positions, float* normals, float* texcoords,
+    int32_t* triangles, int32_t* quads) {
+  if (!s || shape < 0 || shape >= (int)s->scene.shapes.size()) return VPT_ERR_INVALID;
+  auto& sh = s->scene.shapes[shape];
+  if (positions) memcpy(positions, sh.positions.data(), sizeof(vec3f) * sh.positions.size());
+  if (normals) memcpy(normals, sh.normals.data(), sizeof(vec3f) * sh.normals.size());
+  if (texcoords) memcpy(texcoords, sh.texcoords.data(), sizeof(vec2f) * sh.texcoords.size());
+  if (triangles) memcpy(triangles, sh.triangles.data(), sizeof(vec3i) * sh.triangles.size());
+  if (quads) memcpy(quads, sh.quads.data(), sizeof(vec4i) * sh.quads.size());
+  return VPT_OK;
+}
+
 int vpth_scene_use_device_bvh(vpth_scene* s, vpt_bvh_build_stats* total) {
   if (!s) return VPT_ERR_INVALID;
   return guarded([&] {

@@ -3,7 +3,7 @@
 // Same names, argument meaning, defaults and error behaviour as the
 // reference's public header (libs/yocto_pathtrace/yocto_pathtrace.h:57-139):
 // pathtrace_params, pathtrace_state, pathtrace_lights, the shader enum and its
-// names, make_state / make_bvh / make_lights /
+// names, make_state / make_bvh / make_lights / tesselate_surfaces /
 // pathtrace_samples / get_render. trace_samples is an alias of
 // pathtrace_samples (the name BASELINE.json uses). The host builds (BVH, light
 // CDFs, per-pixel generators) run on the CPU as in the reference; everything
@@ -116,11 +116,13 @@ bvh_shape make_bvh_device(const shape_data& shape, vpt_bvh_build_stats* stats = 
 // Light list and sampling CDFs (yocto_pathtrace.cpp:983-1049).
 pathtrace_lights make_lights(const scene_data& scene, const pathtrace_params& params);
 
-// tesselate_surfaces (yocto_pathtrace.h:128) has no counterpart here: a .vptscene archive holds
-// shapes that tools/vpt_export already tessellated with the reference's own host code
-// (Catmull-Clark + displacement is scene preparation, SURVEY 8(f) #3, not on the sample loop).
-// A caller that holds the reference's scene_data calls the reference's tesselate_surfaces and
-// then the adapter of integration/yocto_pathtrace_cuda.cpp.
+// Tesselate subdivs (yocto_pathtrace.h:128, yocto_pathtrace.cpp:1230-1280): Catmull-Clark levels,
+// smooth normals and texture displacement run on the device (vpt_cuda_catmullclark /
+// _vertex_normals / _displace), the face-varying split and triangulation on the host; shapes
+// equal the reference's bit for bit. Archives written by tools/vpt_export without
+// --keep-subdivs arrive tessellated (by the reference's own code) and have no subdivs left.
+void tesselate_surfaces(scene_data& scene);
+void tesselate_surface(shape_data& shape, const subdiv_data& subdiv, const scene_data& scene);
 
 // Progressively computes an image: params.batch samples per call (default 1,
 // as the reference). Blocking. Throws std::runtime_error("sampler unknown") for

@@ -111,6 +111,18 @@ struct sdf_data {
   float    params[4] = {0, 0, 0, 0};
 };
 
+// subdivision surface (yocto_scene.h:161-183): face-varying control cage of shape `shape`
+struct subdiv_data {
+  std::vector<vec4i> quadspos = {}, quadsnorm = {}, quadstexcoord = {};
+  std::vector<vec3f> positions = {}, normals = {};
+  std::vector<vec2f> texcoords = {};
+  int   subdivisions = 0;
+  bool  catmullclark = true, smooth = true;
+  float displacement     = 0;
+  int   displacement_tex = invalidid;
+  int   shape            = invalidid;
+};
+
 struct scene_data {
   std::vector<camera_data>      cameras       = {};
   std::vector<instance_data>    instances     = {};
@@ -121,6 +133,7 @@ struct scene_data {
   std::vector<volume_data>      volumes       = {};
   std::vector<volume_instance>  vol_instances = {};
   std::vector<sdf_data>         sdfs          = {};
+  std::vector<subdiv_data>      subdivs       = {};  // pending: see tesselate_surfaces
 };
 
 // bvh (yocto_bvh.h:73-92); the node is the C ABI's vpt_bvh_node (32 bytes)
@@ -136,5 +149,7 @@ using bvh_shape = bvh_data;
 // Loads a ".vptscene" archive written by tools/vpt_export or by the
 // Python fixture generators (volumetric-path-tracer_b200/archive.py).
 bool load_scene(const std::string& filename, scene_data& scene, std::string& error);
+// the `subdivs` arrays of an archive (tools/vpt_export --keep-subdivs / --dump-subdivs) only
+bool load_subdivs(const std::string& filename, scene_data& scene, std::string& error);
 
 }  // namespace vpt

@@ -18,10 +18,43 @@ static void assign(std::vector<T>& dst, const archive_array* a, size_t per_item_
   if (n) memcpy(dst.data(), a->data.data(), n * sizeof(T));
 }
 
+// subdivs.count + subdiv<i>.{quadspos, quadsnorm, quadstexcoord, positions, normals, texcoords,
+// params = {subdivisions, catmullclark, smooth, displacement_tex, shape}, displacement}
+static bool read_subdivs(const archive& ar, scene_data& scene) {
+  scene.subdivs.clear();
+  auto count = ar.find("subdivs.count");
+  if (!count || count->dtype != dt_i32) return true;
+  for (int i = 0; i < count->i32()[0]; i++) {
+    auto  pre = "subdiv" + std::to_string(i) + ".";
+    auto& s   = scene.subdivs.emplace_back();
+    assign(s.quadspos, ar.find(pre + "quadspos"), 4);
+    assign(s.quadsnorm, ar.find(pre + "quadsnorm"), 4);
+    assign(s.quadstexcoord, ar.find(pre + "quadstexcoord"), 4);
+    assign(s.positions, ar.find(pre + "positions"), 3);
+    assign(s.normals, ar.find(pre + "normals"), 3);
+    assign(s.texcoords, ar.find(pre + "texcoords"), 2);
+    auto params = ar.find(pre + "params"), disp = ar.find(pre + "displacement");
+    if (!params || params->dtype != dt_i32 || params->count() < 5 || !disp) return false;
+    auto q = params->i32();
+    s.subdivisions = q[0], s.catmullclark = q[1] != 0, s.smooth = q[2] != 0;
+    s.displacement_tex = q[3], s.shape = q[4];
+    s.displacement = disp->f32()[0];
+  }
+  return true;
+}
+
+bool load_subdivs(const std::string& filename, scene_data& scene, std::string& error) {
+  auto ar = archive{};
+  if (!ar.load(filename, error)) return false;
+  if (!read_subdivs(ar, scene)) return error = "malformed subdiv arrays in " + filename, false;
+  return true;
+}
+
 bool load_scene(const std::string& filename, scene_data& scene, std::string& error) {
   auto ar = archive{};
   if (!ar.load(filename, error)) return false;
   scene = scene_data{};
+  if (!read_subdivs(ar, scene)) return error = "malformed subdiv arrays in " + filename, false;
   auto missing = [&](const char* name) {
     error = std::string("missing array ") + name + " in " + filename;
     return false;
