@@ -256,6 +256,11 @@ int main(int argc, const char** argv) {
       state = make_state(scene, params);
       bind_device_scene(state, dscene, scene, bvh, lights);
     }
+    if (params.gpus > 1) {
+      t0 = clock();
+      bind_device_replicas(state, scene, bvh, lights, params.gpus);
+      printf("set up %d GPUs: %.3f s\n", params.gpus, since(t0));
+    }
     // The viewer's display loop without a window (apps/ypathtrace/ypathtrace.cpp:156-189): a
     // one-sample preview at resolution / pratio blown up to the frame, then the tonemapped
     // frame every `display_every` samples - tonemap + 8-bit conversion run on the device, the

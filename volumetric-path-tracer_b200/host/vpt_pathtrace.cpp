@@ -5,6 +5,9 @@
 #include "vpt_pathtrace.h"
 
 #include <algorithm>
+#include <array>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <thread>
 
@@ -414,6 +417,12 @@ static void bind_replicas(device_binding& dev, pathtrace_state& state, const sce
     check(vpt_cuda_state_add_peer(dev.state, rep->state), "vpt_cuda_state_add_peer");
 }
 
+void bind_device_replicas(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, int gpus) {
+  if (gpus <= 1) return;
+  bind_replicas(bind(state, scene, bvh, lights), state, scene, bvh, lights, gpus);
+}
+
 void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
     const pathtrace_lights& lights, const pathtrace_params& params) {
   if (state.samples >= params.samples) return;
@@ -439,20 +448,34 @@ void pathtrace_samples(pathtrace_state& state, const scene_data& scene, const bv
   if (cparams.samples != 1) cparams.samples = 1 << 30;
   auto errors  = std::vector<std::string>(gpus);
   auto workers = std::vector<std::thread>{};
+  // VPT_GPUS_TRACE=1: per-rank wall-clock interval of every call (host-thread overlap check)
+  static const bool timeline = getenv("VPT_GPUS_TRACE") != nullptr;
+  auto t0    = std::chrono::steady_clock::now();
+  auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+  auto spans = std::vector<std::array<double, 2>>(gpus, {0, 0});
   for (int r = 1; r < gpus; r++) {
     int share = sample_share(batch, gpus, r);
     if (share <= 0) continue;
     workers.emplace_back([&, r, share] {
-      auto& rep = *dev.replicas[r - 1];
+      auto& rep   = *dev.replicas[r - 1];
+      spans[r][0] = since();
       if (vpt_cuda_set_device(rep.device) != VPT_OK ||
           vpt_cuda_trace_samples(rep.scene, rep.state, &cparams, share) != VPT_OK)
         errors[r] = vpt_cuda_last_error();
+      spans[r][1] = since();
     });
   }
-  int status = vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams,
+  spans[0][0] = since();
+  int status  = vpt_cuda_trace_samples(dev.scene->handle, dev.state, &cparams,
       sample_share(batch, gpus, 0));
+  spans[0][1] = since();
   if (status != VPT_OK) errors[0] = vpt_cuda_last_error();
   for (auto& w : workers) w.join();
+  if (timeline) {
+    for (int r = 0; r < gpus; r++)
+      fprintf(stderr, "[vpt gpus] rank %d: %.1f .. %.1f ms (%d samples)\n", r, spans[r][0], spans[r][1],
+          sample_share(batch, gpus, r));
+  }
   for (auto& e : errors)
     if (!e.empty()) throw std::runtime_error("vpt_cuda_trace_samples: " + e);
   state.samples = vpt_cuda_state_total_samples(dev.state);

@@ -180,6 +180,11 @@ std::shared_ptr<device_scene> upload_scene(
     const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
 void bind_device_scene(pathtrace_state& state, const std::shared_ptr<device_scene>& dscene,
     const scene_data& scene, const bvh_scene& bvh, const pathtrace_lights& lights);
+// Contexts, scene replicas and states of GPUs 1 .. gpus-1 ahead of time (the first
+// pathtrace_samples call with params.gpus > 1 otherwise sets them up: about a second per process
+// for the extra contexts and the module load)
+void bind_device_replicas(pathtrace_state& state, const scene_data& scene, const bvh_scene& bvh,
+    const pathtrace_lights& lights, int gpus);
 vpt_scene* device_handle(const std::shared_ptr<device_scene>& scene);
 vpt_state* device_handle(pathtrace_state& state);
 // the device image was replaced (e.g. by a cross-GPU reduce): state.samples becomes
