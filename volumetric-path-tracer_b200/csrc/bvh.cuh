@@ -94,6 +94,25 @@ struct stack_t {
     *reinterpret_cast<int2_t*>(base + 2 * i * stride) = int2_t{r, f2i(t)};
   }
 };
+// The pooled extend kernel's stack (wavefront.cuh, k_wf_extend_pool): entries [0, limit) in the
+// ray's shared-memory column, deeper ones in a global spill column (the uploader's depth bound
+// is a worst case; walks rarely come near it).
+struct pool_stack_t {
+  int* base;
+  int  stride;
+  int* over;
+  int  ostride, limit;
+  VPT_FN stack_t::entry_t get(int i) const {
+    int2_t v;
+    if (i < limit) v = *reinterpret_cast<const int2_t*>(base + 2 * i * stride);
+    else v = *reinterpret_cast<const int2_t*>(over + 2 * (size_t)(i - limit) * ostride);
+    return {v.x, i2f(v.y)};
+  }
+  VPT_FN void push(int i, int r, float t) const {
+    if (i < limit) *reinterpret_cast<int2_t*>(base + 2 * i * stride) = int2_t{r, f2i(t)};
+    else *reinterpret_cast<int2_t*>(over + 2 * (size_t)(i - limit) * ostride) = int2_t{r, f2i(t)};
+  }
+};
 constexpr int vpt_stack_words = 2;  // ints per entry (sizes the shared-memory columns)
 
 constexpr int vpt_stack_depth = 64;  // uploader rejects deeper trees
@@ -237,7 +256,8 @@ struct trav_t {
   hit_t h;
 
   // `first`: < 0 for the whole scene, else the instance of the instance-targeted query
-  VPT_FN void begin(const DScene& sc, int first, const ray3& ray, stack_t st) {
+  template <class ST>
+  VPT_FN void begin(const DScene& sc, int first, const ray3& ray, ST st) {
     h = hit_t{-1, -1, {0, 0}, 0, false};
     o = ray.o, d = ray.d;
     tmin = ray.tmin, tmax = ray.tmax;
@@ -264,7 +284,8 @@ struct trav_t {
   }
 
   // One visit of a wide node (see the header): four slab tests, pushes in visit order.
-  VPT_FN void visit_wide(const DScene& sc, int e, stack_t st) {
+  template <class ST>
+  VPT_FN void visit_wide(const DScene& sc, int e, ST st) {
     VPT_WORK(wide_visits, 1);
     auto p  = sc.wnodes + 8 * (size_t)e;
     int  sx = oct & 1, sy = (oct >> 1) & 1, sz = oct >> 2;
@@ -310,15 +331,90 @@ struct trav_t {
   // or it has popped `trav_pops` entries; then enter the instance / process the leaf. The
   // bound keeps lanes that already hold work from waiting on the lane with the longest
   // descent; it changes the SIMT schedule only.
-  VPT_FN void round(const DScene& sc, const ray3& ray, stack_t st) {
+  template <class ST>
+  VPT_FN void round(const DScene& sc, const ray3& ray, ST st) {
     int leaf = descend(sc, ray, st);
     if (leaf != 0) test_leaf(sc, leaf);
+  }
+
+  // The four operations of a walk, shared by the bounded descent below and by the phase
+  // machine (fetch / run_*) that the extend kernel elects between.
+  // A binary node: both child boxes, pushed in the reference's order (yocto_bvh.cpp:829-846)
+  template <class ST>
+  VPT_FN void visit_binary(const DScene& sc, int e, ST st) {
+    VPT_WORK(node_visits, 1);
+    auto p  = sc.nodes + 4 * (size_t)e;
+    auto a0 = ld4(p), a1 = ld4(p + 1), b0 = ld4(p + 2), b1 = ld4(p + 3);
+    float ta, tb;
+    bool  pa = intersect_box(o, dinv, tmin, tmax, a0, a1, plain, ta);
+    bool  pb = intersect_box(o, dinv, tmin, tmax, b0, b1, plain, tb);
+    auto  axis = f2i(a1.w);
+    auto  sgn  = (axis == 0 ? dinv.x : (axis == 1 ? dinv.y : dinv.z)) < 0;
+    // reference order: push (c0, c1) if the sign is set, else (c1, c0);
+    // the last pushed child is visited first
+    int   r1 = f2i(sgn ? a1.z : b1.z), r2 = f2i(sgn ? b1.z : a1.z);
+    float t1 = sgn ? ta : tb, t2 = sgn ? tb : ta;
+    bool  p1 = sgn ? pa : pb, p2 = sgn ? pb : pa;
+    if (p1) st.push(cur++, r1, t1);
+    if (p2) st.push(cur++, r2, t2);
+  }
+  template <class ST>
+  VPT_FN void visit_node(const DScene& sc, int e, ST st) {
+    if (wide) visit_wide(sc, e, st);
+    else visit_binary(sc, e, st);
+  }
+  // back to the world-space ray (a sentinel was popped)
+  VPT_FN void leave_instance(const ray3& ray) {
+    o = ray.o, d = ray.d;
+    dinv = wdinv, plain = wplain;
+    wide = wwide, oct = woct;
+    kind = -1;
+  }
+  // transform the ray, test the shape's root box (yocto_bvh.cpp:854-858, :714-722)
+  template <class ST>
+  VPT_FN void enter_instance(const DScene& sc, const ray3& ray, int enter, ST st) {
+    VPT_WORK(inst_transforms, 1);
+    auto t  = sc.inst_trav + 4 * enter;
+    auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
+    if (f2i(c0.w) >= 0) {
+      auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
+      auto r0 = ld4(sc.inst_root + 2 * enter), r1 = ld4(sc.inst_root + 2 * enter + 1);
+      auto lo = transform_point(inv, ray.o);
+      auto ld = transform_vector(inv, ray.d);
+      auto li = f3{1 / ld.x, 1 / ld.y, 1 / ld.z};
+      auto lp = all_finite(li);
+      float t0;
+      if (intersect_box(lo, li, tmin, tmax, r0, r1, lp, t0)) {
+        o = lo, d = ld, dinv = li, plain = lp;
+        wide = lp && all_finite(lo) && f2i(r1.w) != wide_none;
+        oct  = octant(li);
+        inst = enter;
+        kind = f2i(c1.w);
+        st.push(cur++, make_ref(0, ref_sentinel), 0);
+        st.push(cur++, wide ? f2i(r1.w) : f2i(r1.z), t0);
+      }
+    }
+  }
+  // a scene leaf queues its instances (reverse order, so that they pop in leaf order)
+  template <class ST>
+  VPT_FN void queue_instances(const DScene& sc, const ray3& ray, int leaf, ST st) {
+    int lstart = leaf >> 3, lnum = leaf & 7;
+    for (auto i = lnum - 1; i >= 0; i--) {
+      auto p  = sc.scene_leaves + 2 * (lstart + i);
+      auto b0 = ld4(p), b1 = ld4(p + 1);
+      bool skip = cull && omax <= b1.w && misses_instance_box(o, dinv, tmin, tmax, b0, b1);
+#if defined(VPT_CULL_CHECK)
+      if (skip && vpt_cull_check_on) vpt_cull_check(sc, f2i(b1.z), ray, tmax);
+#endif
+      if (!skip) st.push(cur++, make_ref(f2i(b1.z), ref_instance), 0);
+    }
   }
 
   // The descent of one round. Returns the mesh leaf this lane now holds (0: none); the
   // caller tests its primitives, alone (test_leaf) or together with the other lanes of the
   // warp (wavefront.cuh, wf_test_leaves_warp).
-  VPT_FN int descend(const DScene& sc, const ray3& ray, stack_t st) {
+  template <class ST>
+  VPT_FN int descend(const DScene& sc, const ray3& ray, ST st) {
     int leaf = 0, enter = -1;
     int pops = trav_pops;
     VPT_WORK(rounds, 1);
@@ -336,24 +432,8 @@ struct trav_t {
       if (e >= 0) {
         if (!(te <= tmax * box_slack)) {
           VPT_WORK(stale_node_pops, 1);
-        } else if (wide) {
-          visit_wide(sc, e, st);
         } else {
-          VPT_WORK(node_visits, 1);
-          auto p  = sc.nodes + 4 * (size_t)e;
-          auto a0 = ld4(p), a1 = ld4(p + 1), b0 = ld4(p + 2), b1 = ld4(p + 3);
-          float ta, tb;
-          bool  pa = intersect_box(o, dinv, tmin, tmax, a0, a1, plain, ta);
-          bool  pb = intersect_box(o, dinv, tmin, tmax, b0, b1, plain, tb);
-          auto  axis = f2i(a1.w);
-          auto  sgn  = (axis == 0 ? dinv.x : (axis == 1 ? dinv.y : dinv.z)) < 0;
-          // reference order: push (c0, c1) if the sign is set, else (c1, c0);
-          // the last pushed child is visited first
-          int   r1 = f2i(sgn ? a1.z : b1.z), r2 = f2i(sgn ? b1.z : a1.z);
-          float t1 = sgn ? ta : tb, t2 = sgn ? tb : ta;
-          bool  p1 = sgn ? pa : pb, p2 = sgn ? pb : pa;
-          if (p1) st.push(cur++, r1, t1);
-          if (p2) st.push(cur++, r2, t2);
+          visit_node(sc, e, st);
         }
       } else {
         int x = ~e, tag = x & 3;
@@ -369,54 +449,64 @@ struct trav_t {
       }
     }
     again = false;
-    if (enter == -2) {  // back to the world-space ray
-      o = ray.o, d = ray.d;
-      dinv = wdinv, plain = wplain;
-      wide = wwide, oct = woct;
-      kind = -1;
+    if (enter == -2) {
+      leave_instance(ray);
       enter = -1;
       again = cur != 0 && pops != 0;
     }
     }
-    if (enter >= 0) {
-      // transform the ray, test the shape's root box (yocto_bvh.cpp:854-858, :714-722)
-      VPT_WORK(inst_transforms, 1);
-      auto t  = sc.inst_trav + 4 * enter;
-      auto c0 = ld4(t), c1 = ld4(t + 1), c2 = ld4(t + 2), c3 = ld4(t + 3);
-      if (f2i(c0.w) >= 0) {
-        auto inv = frame3{xyz(c0), xyz(c1), xyz(c2), xyz(c3)};
-        auto r0 = ld4(sc.inst_root + 2 * enter), r1 = ld4(sc.inst_root + 2 * enter + 1);
-        auto lo = transform_point(inv, ray.o);
-        auto ld = transform_vector(inv, ray.d);
-        auto li = f3{1 / ld.x, 1 / ld.y, 1 / ld.z};
-        auto lp = all_finite(li);
-        float t0;
-        if (intersect_box(lo, li, tmin, tmax, r0, r1, lp, t0)) {
-          o = lo, d = ld, dinv = li, plain = lp;
-          wide = lp && all_finite(lo) && f2i(r1.w) != wide_none;
-          oct  = octant(li);
-          inst = enter;
-          kind = f2i(c1.w);
-          st.push(cur++, make_ref(0, ref_sentinel), 0);
-          st.push(cur++, wide ? f2i(r1.w) : f2i(r1.z), t0);
-        }
-      }
-    }
-    // a scene leaf queues its instances (reverse order, so that they pop in leaf order)
+    if (enter >= 0) enter_instance(sc, ray, enter, st);
     if (leaf != 0 && kind < 0) {
-      int lstart = leaf >> 3, lnum = leaf & 7;
-      for (auto i = lnum - 1; i >= 0; i--) {
-        auto p  = sc.scene_leaves + 2 * (lstart + i);
-        auto b0 = ld4(p), b1 = ld4(p + 1);
-        bool skip = cull && omax <= b1.w && misses_instance_box(o, dinv, tmin, tmax, b0, b1);
-#if defined(VPT_CULL_CHECK)
-        if (skip && vpt_cull_check_on) vpt_cull_check(sc, f2i(b1.z), ray, tmax);
-#endif
-        if (!skip) st.push(cur++, make_ref(f2i(b1.z), ref_instance), 0);
-      }
+      queue_instances(sc, ray, leaf, st);
       leaf = 0;
     }
     return leaf;
+  }
+
+  // ---- The same walk as a phase machine (k_wf_extend_persistent) ----
+  // fetch() pops until the lane holds one of the three expensive operations - a node visit, an
+  // instance entry, a mesh leaf - or its stack is empty or `pops` entries are gone; the cheap
+  // ones (stale entries, sentinels, scene leaves) are done on the way. The kernel then runs
+  // ONE kind of operation for all the lanes of the warp that hold it (run_node / run_instance
+  // / test_leaf). Per ray this is the sequence of operations of descend(): only the SIMT
+  // schedule differs, hits are bit-identical.
+  static constexpr int op_none = 0, op_node = 1, op_leaf = 2, op_instance = 3;
+  template <class ST>
+  VPT_FN int fetch(const DScene& sc, const ray3& ray, ST st, int pops, int& arg) {
+    while (cur != 0 && pops != 0) {
+      pops--;
+      VPT_WORK(pops, 1);
+      auto  en = st.get(--cur);
+      int   e  = en.ref;
+      float te = en.t0;
+      if (e >= 0) {
+        if (te <= tmax * box_slack) {
+          arg = e;
+          return op_node;
+        }
+        VPT_WORK(stale_node_pops, 1);
+      } else {
+        int x = ~e, tag = x & 3;
+        if (tag == ref_leaf) {
+          VPT_WORK(leaf_pops, 1);
+          if (te <= tmax * box_slack) {
+            if (kind >= 0) {
+              arg = x >> 2;
+              return op_leaf;
+            }
+            queue_instances(sc, ray, x >> 2, st);
+          } else {
+            VPT_WORK(stale_pops, 1);
+          }
+        } else if (tag == ref_instance) {
+          arg = x >> 2;
+          return op_instance;
+        } else {
+          leave_instance(ray);
+        }
+      }
+    }
+    return op_none;
   }
 
   // mesh leaf: primitives in stored order, `t <= tmax` accepts
@@ -482,8 +572,17 @@ VPT_FN hit_t intersect_instance(const DScene& sc, int instance, const ray3& ray,
 }
 
 // Closest hit over the whole scene (yocto_bvh.cpp:800-871).
+#if defined(VPT_RAY_SINK) && !defined(__CUDACC__)
+}  // namespace vpt
+#include <vector>
+namespace vpt {
+inline std::vector<ray3>* vpt_ray_sink = nullptr;  // tests/hostsim/warpsim: every scene query
+#endif
 VPT_FN hit_t intersect_scene(const DScene& sc, const ray3& ray, stack_t st) {
   VPT_WORK(scene_queries, 1);
+#if defined(VPT_RAY_SINK) && !defined(__CUDACC__)
+  if (vpt_ray_sink) vpt_ray_sink->push_back(ray);
+#endif
   return traverse(sc, -1, ray, st);
 }
 

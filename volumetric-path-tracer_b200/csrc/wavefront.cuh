@@ -542,6 +542,12 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
   bool     more    = true;   // warp-uniform: the queue may still hold unclaimed entries
   bool     running = true;   // warp-uniform, the only exit
   int      resumed = 0;
+#if defined(VPT_EXT_ELECT)
+  int held = 0, held_arg = 0;  // the operation this lane's ray holds (trav_t::op_*)
+#if !defined(VPT_ELECT_POPS)
+#define VPT_ELECT_POPS 3
+#endif
+#endif
   // Measured on B200: parking pays for sphere tracing (07_sdfunction 136 -> 100 ms
   // per 16 spp), not for BVH walks, whose parked state is 20x larger and whose pixels' tail
   // then lasts more iterations (03_volume 209 -> 217 ms); -DVPT_WF_SUSPEND_MESH opts in.
@@ -591,7 +597,24 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
       for (int k = 0; k < wf_sdf_steps; k++)
         if (has_ray && !sp.done()) sp.step(sc, ray, prm.spheretrace_maxiter);
     } else {
-#if !defined(VPT_WF_COOP_LEAVES)
+#if defined(VPT_EXT_ELECT)
+      // Election (tests/hostsim/warpsim "elect"): every lane pops until it holds a node visit,
+      // an instance entry or a mesh leaf; the warp then runs the operation most lanes hold, and
+      // any other that VPT_EXT_ELECT lanes hold. The others keep theirs for a later round.
+      if (has_ray && held == 0 && !t.done()) held = t.fetch(sc, ray, st, VPT_ELECT_POPS, held_arg);
+      {
+        int cn = __popc(__ballot_sync(full, has_ray && held == trav_t::op_node));
+        int ci = __popc(__ballot_sync(full, has_ray && held == trav_t::op_instance));
+        int cl = __popc(__ballot_sync(full, has_ray && held == trav_t::op_leaf));
+        int best = cn > ci ? (cn > cl ? cn : cl) : (ci > cl ? ci : cl);
+        if (has_ray && held == trav_t::op_node && (cn == best || cn >= VPT_EXT_ELECT))
+          t.visit_node(sc, held_arg, st), held = 0;
+        if (has_ray && held == trav_t::op_instance && (ci == best || ci >= VPT_EXT_ELECT))
+          t.enter_instance(sc, ray, held_arg, st), held = 0;
+        if (has_ray && held == trav_t::op_leaf && (cl == best || cl >= VPT_EXT_ELECT))
+          t.test_leaf(sc, held_arg), held = 0;
+      }
+#elif !defined(VPT_WF_COOP_LEAVES)
       if (has_ray && !t.done()) t.round(sc, ray, st);
 #else
       int leaf = 0;
@@ -599,7 +622,11 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
       wf_test_leaves_warp(sc, t, leaf, leaf_tab[threadIdx.x >> 5]);
 #endif
     }
+#if defined(VPT_EXT_ELECT)
+    bool     retire   = has_ray && (sdf ? sp.done() : (t.done() && held == 0));
+#else
     bool     retire   = has_ray && (sdf ? sp.done() : t.done());
+#endif
     unsigned retiring = __ballot_sync(full, retire);
     if (retire) {
       isect_t isec;
@@ -662,6 +689,275 @@ __global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
   }
   for (int o = 16; o > 0; o >>= 1) resumed += __shfl_down_sync(full, resumed, o);
   if (lane == 0 && resumed) atomicAdd(&w.counters->rays_resumed, (unsigned long long)resumed);
+}
+
+// ---- Pooled extend (mesh shaders) -------------------------------------------------
+// k_wf_extend_persistent keeps one ray per lane in registers, so at any instruction the lanes of
+// a warp are spread over the walk's operations (node visit / instance entry / leaf test / pops):
+// ncu r02c counts 7.7 of 32 lanes per instruction, and tests/hostsim/warpsim reproduces it from
+// the rays alone. Here a warp owns a POOL of wf_pool_k * 32 rays whose state lives in shared
+// memory. Every round it counts how many of its rays hold each kind of operation, and for every
+// kind that enough rays hold (else for the one most rays hold) it compacts up to 32 of those
+// rays onto its lanes, runs that one operation for all of them, pops each ray's next stack
+// entry to find what it holds next, and writes the changed fields back. Per ray the operations
+// and their order are those of trav_t::descend (the same member functions run them): hits are
+// bit-identical, only the SIMT schedule differs.
+// Shared memory per ray: 19 words of state + `limit` stack entries; deeper entries (the
+// uploader's depth bound is a worst case) go to a global spill column.
+#if !defined(VPT_POOL_K)
+#define VPT_POOL_K 3
+#endif
+#if !defined(VPT_POOL_BLOCKS)
+#define VPT_POOL_BLOCKS 3
+#endif
+#if !defined(VPT_POOL_RUN_AT)
+#define VPT_POOL_RUN_AT 24
+#endif
+constexpr int wf_pool_k = VPT_POOL_K;  // rays per lane of a warp's pool
+enum : int {
+  pf_ox, pf_oy, pf_oz, pf_dx, pf_dy, pf_dz, pf_ix, pf_iy, pf_iz,  // ray in the current space, 1 / d
+  pf_wix, pf_wiy, pf_wiz,                                        // 1 / d of the world-space ray
+  pf_tmax, pf_inst, pf_hinst, pf_arg, pf_qidx, pf_slot, pf_ctl,
+  pf_fields
+};
+// pf_ctl: what the ray holds (3 bits) | stack height (7) | kind + 1 (2) | plain | wide | oct (3)
+//         | wplain | wwide | woct (3) | cull | hit | in-volume
+constexpr int pc_pop = 0,    // nothing yet: pop
+              pc_node = 1,   // a node to visit
+              pc_leaf = 2,   // a mesh leaf to test
+              pc_inst = 3,   // an instance to enter
+              pc_done = 4,   // walk over: retire
+              pc_sleaf = 5,  // a scene leaf: queue its instances
+              pc_idle = 7;
+constexpr int pc_hit = 1 << 23, pc_vol = 1 << 24;
+__device__ __forceinline__ int pool_pack(const trav_t& t, int op, int keep) {
+  return op | (t.cur << 3) | ((t.kind + 1) << 10) | (t.plain ? 1 << 12 : 0) | (t.wide ? 1 << 13 : 0) |
+         (t.oct << 14) | (t.wplain ? 1 << 17 : 0) | (t.wwide ? 1 << 18 : 0) | (t.woct << 19) |
+         (t.cull ? 1 << 22 : 0) | (keep & (pc_hit | pc_vol));
+}
+__device__ __forceinline__ void pool_unpack(trav_t& t, int ctl) {
+  t.cur = (ctl >> 3) & 127, t.kind = ((ctl >> 10) & 3) - 1;
+  t.plain = (ctl >> 12) & 1, t.wide = (ctl >> 13) & 1, t.oct = (ctl >> 14) & 7;
+  t.wplain = (ctl >> 17) & 1, t.wwide = (ctl >> 18) & 1, t.woct = (ctl >> 19) & 7;
+  t.cull = (ctl >> 22) & 1;
+  t.tmin = 1e-4f;  // make_ray
+}
+
+template <int S>
+__global__ void __launch_bounds__(wf_block, VPT_POOL_BLOCKS)
+    k_wf_extend_pool(const DScene sc, const DParams prm, wf_view w, int cur, int limit) {
+  extern __shared__ int pool_mem[];
+  constexpr int      K    = wf_pool_k;
+  constexpr int      BR   = wf_block * K;  // rays per block
+  const unsigned     full = 0xffffffffu;
+  float*             state = reinterpret_cast<float*>(pool_mem);       // [pf_fields][BR]
+  int*               stack = pool_mem + pf_fields * BR;                // [limit][BR] entries
+  unsigned char*     ids   = reinterpret_cast<unsigned char*>(stack + 2 * limit * BR) + (threadIdx.x >> 5) * 32 * K;
+  const int          lane  = threadIdx.x & 31;
+  const int          r0    = (threadIdx.x >> 5) * 32 * K;  // this warp's rays: [r0, r0 + 32 K)
+  const unsigned     lt    = (1u << lane) - 1;
+  const int          count = w.counters->count_ext[cur];
+  int*               spill = reinterpret_cast<int*>(w.susp[0]);
+  const int          ostride = gridDim.x * BR;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    w.counters->count_pdf = 0;
+    w.counters->rays_extend += (unsigned long long)count;
+  }
+#define PF(f, r) state[(f) * BR + (r)]
+#define PI(f, r) reinterpret_cast<int*>(state)[(f) * BR + (r)]
+  // What the ray holds next: pops until one of the operations turns up (at most 3 entries; a
+  // ray that still has nothing goes to the pop round). Stale entries are dropped and a sentinel
+  // restores the world-space ray on the way. Writes pf_arg and pf_ctl.
+  auto next_op = [&](trav_t& t, int r, const pool_stack_t& st, int ctl) {
+    int op = pc_pop, arg = 0;
+    for (int it = 0; it < 3 && op == pc_pop && t.cur != 0; it++) {
+      auto  en = st.get(--t.cur);
+      int   e  = en.ref;
+      float te = en.t0;
+      if (e >= 0) {
+        if (te <= t.tmax * box_slack) op = pc_node, arg = e;
+      } else {
+        int x = ~e, tag = x & 3;
+        if (tag == ref_leaf) {
+          if (te <= t.tmax * box_slack)
+            op = t.kind < 0 ? pc_sleaf : pc_leaf, arg = x >> 2;
+        } else if (tag == ref_instance) {
+          op = pc_inst, arg = x >> 2;
+        } else {
+          // sentinel: back to the world-space ray (kept in the slot record)
+          int  slot = PI(pf_slot, r);
+          auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
+          PF(pf_ox, r) = a0.x, PF(pf_oy, r) = a0.y, PF(pf_oz, r) = a0.z;
+          PF(pf_dx, r) = a0.w, PF(pf_dy, r) = a1.x, PF(pf_dz, r) = a1.y;
+          PF(pf_ix, r) = PF(pf_wix, r), PF(pf_iy, r) = PF(pf_wiy, r), PF(pf_iz, r) = PF(pf_wiz, r);
+          t.plain = t.wplain, t.wide = t.wwide, t.oct = t.woct;
+          t.kind  = -1;
+        }
+      }
+    }
+    if (op == pc_pop && t.cur == 0) op = pc_done;
+    PI(pf_arg, r) = arg;
+    PI(pf_ctl, r) = pool_pack(t, op, ctl);
+  };
+  for (int k = 0; k < K; k++) PI(pf_ctl, r0 + k * 32 + lane) = pc_idle;
+  __syncwarp();
+  bool more = count > 0;
+  while (true) {
+    // what every ray of the pool holds: one 8-bit counter per kind, two warp reductions
+    int      cat[K];
+    unsigned lo = 0, hi = 0;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+      cat[k] = PI(pf_ctl, r0 + k * 32 + lane) & 7;
+      lo += cat[k] < 4 ? 1u << (8 * cat[k]) : 0u;
+      hi += cat[k] >= 4 ? 1u << (8 * (cat[k] - 4)) : 0u;
+    }
+    lo = __reduce_add_sync(full, lo), hi = __reduce_add_sync(full, hi);
+    if (!more) hi &= 0x00ffffffu;  // nothing left to refill with
+    if ((lo | hi) == 0) break;
+    // the kinds to run this round: every kind that VPT_POOL_RUN_AT rays hold (byte-parallel
+    // compare of the eight counters), else those that half as many hold, else the fullest
+    auto at_least = [&](unsigned t) {
+      unsigned a = ((lo | 0x80808080u) - t * 0x01010101u) & 0x80808080u;
+      unsigned b = ((hi | 0x80808080u) - t * 0x01010101u) & 0x80808080u;
+      // bit 7 of byte c -> bit c (lo), bit c + 4 (hi)
+      a = (a >> 7) * 0x00204081u >> 21 & 15u;  // gathers bits 0, 8, 16, 24 into bits 0..3
+      b = (b >> 7) * 0x00204081u >> 21 & 15u;
+      return a | (b << 4);
+    };
+    unsigned run = at_least(VPT_POOL_RUN_AT);
+    if (run == 0) run = at_least(VPT_POOL_RUN_AT / 2);
+    if (run == 0) {
+      int best = 0, best_kind = 0;
+#pragma unroll
+      for (int c = 0; c < 8; c++) {
+        int n = (int)(((c < 4 ? lo : hi) >> (8 * (c & 3))) & 255u);
+        if (n > best) best = n, best_kind = c;
+      }
+      run = 1u << best_kind;
+    }
+    while (run) {
+      const int pick = __ffs(run) - 1;
+      run &= run - 1;
+      // compact the rays holding it onto the lanes
+      int n = 0;
+#pragma unroll
+      for (int k = 0; k < K; k++) {
+        unsigned b = __ballot_sync(full, cat[k] == pick);
+        if (cat[k] == pick) ids[n + __popc(b & lt)] = (unsigned char)(k * 32 + lane);
+        n += __popc(b);
+      }
+      __syncwarp();
+      int take = n < 32 ? n : 32;
+      int qbase = 0;
+      if (pick == pc_idle) {
+        if (lane == 0) qbase = atomicAdd(&w.counters->ext_head, take);
+        qbase = __shfl_sync(full, qbase, 0);
+        more  = qbase + take < count;
+        take  = count - qbase < take ? (count - qbase > 0 ? count - qbase : 0) : take;
+      }
+      const bool act = lane < take;
+      const int  r   = r0 + (act ? ids[lane] : 0);
+      const auto st  = pool_stack_t{stack + 2 * r, BR, spill + 2 * ((size_t)blockIdx.x * BR + r), ostride, limit};
+      if (pick == pc_done) {  // write the hit, count the shade class; the entry takes a new ray
+        unsigned retiring = __ballot_sync(full, act);
+        if (act) {
+          int  ctl  = PI(pf_ctl, r);
+          int  slot = PI(pf_slot, r);
+          bool hit  = (ctl & pc_hit) != 0;
+          if (!hit) w.at(wf_hit, slot) = {i2f(-1), i2f(-1), 0, 0};
+          w.at(wf_hit1, slot) = {hit ? PF(pf_tmax, r) : 0.0f, i2f(hit ? 1 : 0), 0, 0};
+          int cls = 0;
+          if (hit) {
+            int material = f2i(ld4(sc.inst_trav + 4 * PI(pf_hinst, r) + 3).w);
+            cls = 2 + (material < wf_classes - 4 ? material : wf_classes - 4);
+            if (S == shader_volpathtrace && (ctl & pc_vol)) cls = 1;
+          }
+          unsigned peers  = __match_any_sync(retiring, cls);
+          int      leader = __ffs(peers) - 1;
+          int      base   = 0;
+          if (lane == leader) base = atomicAdd(&w.counters->class_count[cls], __popc(peers));
+          base = __shfl_sync(peers, base, leader);
+          w.sort_key[PI(pf_qidx, r)] = (cls << 24) | (base + __popc(peers & lt));
+          PI(pf_ctl, r) = pc_idle;
+        }
+        if (more) {
+          if (lane == 0) qbase = atomicAdd(&w.counters->ext_head, take);
+          qbase = __shfl_sync(full, qbase, 0);
+          more  = qbase + take < count;
+          take  = count - qbase < take ? (count - qbase > 0 ? count - qbase : 0) : take;
+        } else {
+          take = 0;
+        }
+      }
+      if (pick == pc_done || pick == pc_idle) {
+        if (lane < take) {
+          trav_t t;
+          int  qidx = qbase + lane;
+          int  slot = w.queue_ext[cur][qidx];
+          auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
+          auto ray = make_ray({a0.x, a0.y, a0.z}, {a0.w, a1.x, a1.y});
+          t.begin(sc, -1, ray, st);
+          PF(pf_ox, r) = t.o.x, PF(pf_oy, r) = t.o.y, PF(pf_oz, r) = t.o.z;
+          PF(pf_dx, r) = t.d.x, PF(pf_dy, r) = t.d.y, PF(pf_dz, r) = t.d.z;
+          PF(pf_ix, r) = t.dinv.x, PF(pf_iy, r) = t.dinv.y, PF(pf_iz, r) = t.dinv.z;
+          PF(pf_wix, r) = t.dinv.x, PF(pf_wiy, r) = t.dinv.y, PF(pf_wiz, r) = t.dinv.z;
+          PF(pf_tmax, r) = t.tmax;
+          PI(pf_inst, r) = -1, PI(pf_hinst, r) = -1;
+          PI(pf_qidx, r) = qidx, PI(pf_slot, r) = slot;
+          next_op(t, r, st, (f2i(a1.z) & wf_bit_vol) ? pc_vol : 0);
+        }
+      } else if (act) {
+        trav_t t;
+        int    ctl = 0;
+        {
+          ctl = PI(pf_ctl, r);
+          pool_unpack(t, ctl);
+          t.tmax = PF(pf_tmax, r);
+          if (pick == pc_node) {
+            t.o    = {PF(pf_ox, r), PF(pf_oy, r), PF(pf_oz, r)};
+            t.dinv = {PF(pf_ix, r), PF(pf_iy, r), PF(pf_iz, r)};
+            t.visit_node(sc, PI(pf_arg, r), st);
+          } else if (pick == pc_sleaf) {
+            // the ray is the world-space ray at the scene level
+            t.o    = {PF(pf_ox, r), PF(pf_oy, r), PF(pf_oz, r)};
+            t.dinv = {PF(pf_ix, r), PF(pf_iy, r), PF(pf_iz, r)};
+            t.omax = fmaxf(fmaxf(fabsf(t.o.x), fabsf(t.o.y)), fabsf(t.o.z));
+            t.queue_instances(sc, ray3{}, PI(pf_arg, r), st);
+          } else if (pick == pc_inst) {
+            auto ray = ray3{{PF(pf_ox, r), PF(pf_oy, r), PF(pf_oz, r)},
+                {PF(pf_dx, r), PF(pf_dy, r), PF(pf_dz, r)}, t.tmin, 0};
+            t.o = ray.o, t.d = ray.d, t.dinv = {0, 0, 0};
+            int enter = PI(pf_arg, r);
+            t.enter_instance(sc, ray, enter, st);
+            if (t.kind >= 0) {
+              PF(pf_ox, r) = t.o.x, PF(pf_oy, r) = t.o.y, PF(pf_oz, r) = t.o.z;
+              PF(pf_dx, r) = t.d.x, PF(pf_dy, r) = t.d.y, PF(pf_dz, r) = t.d.z;
+              PF(pf_ix, r) = t.dinv.x, PF(pf_iy, r) = t.dinv.y, PF(pf_iz, r) = t.dinv.z;
+              PI(pf_inst, r) = enter;
+            }
+          } else if (pick == pc_leaf) {
+            t.o    = {PF(pf_ox, r), PF(pf_oy, r), PF(pf_oz, r)};
+            t.d    = {PF(pf_dx, r), PF(pf_dy, r), PF(pf_dz, r)};
+            t.inst = PI(pf_inst, r);
+            t.h    = hit_t{-1, -1, {0, 0}, 0, false};
+            t.test_leaf(sc, PI(pf_arg, r));
+            if (t.h.hit) {
+              PF(pf_tmax, r)  = t.h.distance;
+              PI(pf_hinst, r) = t.h.instance;
+              w.at(wf_hit, PI(pf_slot, r)) = {i2f(t.h.instance), i2f(t.h.element), t.h.uv.x, t.h.uv.y};
+              ctl |= pc_hit;
+            }
+          }
+          // pc_pop: nothing to run, just look further down the stack
+        }
+        next_op(t, r, st, ctl);
+      }
+      __syncwarp();
+    }
+  }
+#undef PF
+#undef PI
 }
 
 // scatter the extend queue into class order (counting sort, second pass)
@@ -951,6 +1247,46 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     if (blocks_env && atoi(blocks_env) > 0 && atoi(blocks_env) < per_sm) resident = atoi(blocks_env) * sms;
     if (resident <= 0) persistent = false;
   }
+  // pooled extend (mesh shaders; VPT_WF_POOL=0 keeps the ray-per-lane kernel): shared memory
+  // per block = ray state + as many stack entries as fit, the rest of the depth bound spills
+  bool pooled = persistent && !is_sdf_shader<S>() && !trace;
+  {
+    const char* pool_env = getenv("VPT_WF_POOL");  // read per call (tests run both kernels)
+    if (!pool_env || atoi(pool_env) == 0) pooled = false;
+  }
+  int    pool_limit = 0, pool_resident = 0;
+  size_t pool_smem  = 0;
+  if (pooled) {
+    constexpr int BR = wf_block * wf_pool_k;
+    int device = 0, sms = 0, smem_sm = 0;
+    cudaGetDevice(&device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
+    const char* pb_env = getenv("VPT_WF_POOL_BLOCKS");  // resident blocks per SM to size for
+    const char* pl_env = getenv("VPT_WF_POOL_LIMIT");   // tests: stack entries kept in shared memory
+    int    want   = pb_env && atoi(pb_env) > 0 ? atoi(pb_env) : VPT_POOL_BLOCKS;
+    size_t fixed  = sizeof(int) * pf_fields * BR + 32 * wf_pool_k * (wf_block / 32);
+    size_t budget = (size_t)smem_sm / want - 1024 - 256;
+    pool_limit    = budget > fixed ? (int)((budget - fixed) / (sizeof(int) * 2 * BR)) : 0;
+    if (pool_limit > scene.stack_depth) pool_limit = scene.stack_depth;
+    if (pl_env && atoi(pl_env) > 0 && atoi(pl_env) < pool_limit) pool_limit = atoi(pl_env);
+    if (pool_limit < 1) pooled = false;
+    if (pooled) {
+      pool_smem = fixed + sizeof(int) * 2 * BR * (size_t)pool_limit;
+      e = cudaFuncSetAttribute(k_wf_extend_pool<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pool_smem);
+      if (e != cudaSuccess) return e;
+      int per_sm = 0;
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend_pool<S>, wf_block, pool_smem);
+      if (e != cudaSuccess) return e;
+      pool_resident = per_sm * sms;
+      if (pool_resident <= 0) pooled = false;
+    }
+    if (pooled) {
+      int spill = scene.stack_depth - pool_limit;
+      e = wf.reserve_suspended(pool_resident * BR, spill > 0 ? (spill + 1) / 2 : 1);
+      if (e != cudaSuccess) return e;
+    }
+  }
   // lanes still walking at or below which a warp parks its rays once the queue is empty
   const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
@@ -991,7 +1327,11 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     auto& w = p.view;
     if (timed) cudaEventRecord(wf.k0, p.stream);
     if (trace) trace->mark(grid);
-    if (persistent)
+    if (pooled) {
+      int blocks = (grid + wf_pool_k - 1) / wf_pool_k;
+      k_wf_extend_pool<S><<<blocks < pool_resident ? blocks : pool_resident, wf_block, pool_smem, p.stream>>>(
+          scene.d, prm, w, p.cur, pool_limit);
+    } else if (persistent)
       k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
           scene.d, prm, w, p.cur, suspend_at);
     else
@@ -1029,8 +1369,9 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     full = (full + (1 << cls) - 1) >> cls;
     if (full < need) return nullptr;
     key.d = scene.d, key.prm = prm, key.view = p.view, key.image = image, key.rngs = rngs;
-    key.suspend_at = suspend_at, key.resident = resident, key.grid = full, key.shader = S;
-    key.persistent = persistent, key.smem = smem;
+    key.suspend_at = pooled ? pool_limit : suspend_at, key.resident = pooled ? pool_resident : resident;
+    key.grid = full, key.shader = S;
+    key.persistent = (persistent ? 1 : 0) | (pooled ? 2 : 0), key.smem = pooled ? pool_smem : smem;
     auto& exec = p.graph[cls];
     auto& kept = p.graph_key[cls];
     if (exec && kept.size() == sizeof(key) && !memcmp(kept.data(), &key, sizeof(key))) return exec;
