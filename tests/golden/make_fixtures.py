@@ -37,6 +37,7 @@ GOLDEN_RENDERS = [
     ("mixed", "eyelight", 2, 64, 4), ("mixed", "naive", 2, 64, 4), ("mixed", "pathtrace", 2, 64, 4),
     ("mixed", "volpathtrace", 2, 64, 8),
     ("sdf_small", "implicit_normal", 1, 64, 4), ("sdf_small", "implicit", 2, 64, 4),
+    ("skewed", "color", 1, 64, 4), ("skewed", "pathtrace", 2, 64, 4),
 ]
 
 
@@ -324,6 +325,45 @@ def build_dark():
     return a
 
 
+def frame_matrix(m, o):
+    m = np.asarray(m, dtype=np.float64)
+    return f32(np.concatenate([m[:, 0], m[:, 1], m[:, 2], np.asarray(o, dtype=np.float64)]))
+
+
+def build_skewed():
+    """Instances with strongly anisotropic and sheared frames (condition numbers 1 ... ~700): the
+    object-space rays of the reference lose eps * cond of precision there, which is what the
+    uploader's culling margin has to cover (csrc/upload.cuh cull_record)."""
+    a = {"meta": np.asarray([1, 0, 0, 0], np.int32)}
+    a["cameras"] = f32(np.stack([camera((0.0, 1.0, 3.4), (0, 0.25, 0))]))
+    add_textures(a, [])
+    add_shapes(a, [quad_shape(2.5), icosphere(2, 0.5), cubesphere(4, 0.35, np.random.default_rng(5))])
+    mats = [material(MATTE, color=(0.7, 0.7, 0.7)), material(GLOSSY, color=(0.7, 0.3, 0.2), roughness=0.2),
+            material(MATTE, color=(0.2, 0.6, 0.3)), material(REFLECTIVE, color=(0.8, 0.8, 0.9), roughness=0.05),
+            material(MATTE, color=(0.9, 0.9, 0.9), emission=(6, 6, 5))]
+    a["materials.f"] = f32(np.stack([m[0] for m in mats]))
+    a["materials.i"] = np.stack([m[1] for m in mats]).astype(np.int32)
+    ry = lambda t: np.array([[np.cos(t), 0, np.sin(t)], [0, 1, 0], [-np.sin(t), 0, np.cos(t)]])
+    shear = np.array([[1.0, 0.9, 0.3], [0.0, 1.0, 0.6], [0.0, 0.0, 1.0]])
+    inst = [(frame(), 0, 0),
+            (frame_matrix(ry(0.3) @ np.diag([2.0, 0.02, 1.0]), (-0.8, 0.3, 0.2)), 1, 1),      # 100 : 1 pancake
+            (frame_matrix(ry(-0.5) @ np.diag([0.015, 1.5, 0.015]), (0.1, 0.8, -0.3)), 1, 2),  # 100 : 1 needle
+            (frame_matrix(ry(0.8) @ shear @ np.diag([1.0, 0.05, 0.6]), (0.9, 0.35, 0.3)), 2, 3),  # sheared slab
+            (frame_matrix(shear.T @ np.diag([0.01, 1.0, 1.0]), (-0.2, 0.6, 0.9)), 2, 1),      # sheared sheet
+            (frame_matrix(ry(0.2) @ np.diag([3.0, 0.004, 3.0]), (0.0, 1.9, 0.0)), 1, 4),      # 750 : 1 light
+            (frame((0.5, 0.25, 0.9)), 2, 2)]
+    a["instances.frame"] = f32(np.stack([i[0] for i in inst]))
+    a["instances.ids"] = np.asarray([[i[1], i[2]] for i in inst], np.int32)
+    a["environments.f"] = f32([np.concatenate([frame(), f32([0.3, 0.3, 0.35])])])
+    a["environments.i"] = np.asarray([[-1]], np.int32)
+    a["volumes.count"] = np.asarray([0], np.int32)
+    a["vol_instances.f"] = np.zeros((0, 13), np.float32)
+    a["vol_instances.i"] = np.zeros((0, 2), np.int32)
+    a["sdfs.f"] = np.zeros((0, 19), np.float32)
+    a["sdfs.i"] = np.zeros((0, 2), np.int32)
+    return a
+
+
 def main():
     import __graft_entry__ as entry
     import util
@@ -332,7 +372,8 @@ def main():
     vpt.archive.save(os.path.join(HERE, "mixed.vptscene"), build_mixed())
     vpt.archive.save(os.path.join(HERE, "sdf_small.vptscene"), build_sdf_small())
     vpt.archive.save(os.path.join(HERE, "dark.vptscene"), build_dark())
-    print("wrote mixed.vptscene, sdf_small.vptscene, dark.vptscene")
+    vpt.archive.save(os.path.join(HERE, "skewed.vptscene"), build_skewed())
+    print("wrote mixed.vptscene, sdf_small.vptscene, dark.vptscene, skewed.vptscene")
     if "--scenes" in sys.argv:
         return
     if not util.have_ref():

@@ -100,6 +100,21 @@ def test_cameras_on_host_match_oracle(vpt, hostsim, tmp_path, camera):
     assert np.array_equal(got["rngs_after"], ref["rngs_after"])
 
 
+def test_first_hits_on_skewed_frames_match_oracle(vpt, hostsim, tmp_path):
+    """Grazing and ordinary rays against 100 : 1 scaled and sheared instances: device headers on the
+    host vs the live oracle, ids and float bits."""
+    if not util.have_ref():
+        pytest.skip("oracle/_ref/ref_render not built")
+    rays = util.camera_rays(0, 0, np.random.default_rng(17), 20000)
+    rp, out = str(tmp_path / "rays.vptarch"), str(tmp_path / "hits.vptarch")
+    vpt.archive.save(rp, {"rays": rays})
+    run_tool(hostsim, "skewed", out, "--rays", rp)
+    got, ref = vpt.archive.load(out), util.oracle_hits(vpt, "skewed", rays)
+    assert ref["hits.ids"][:, 0].sum() > 1000
+    assert np.array_equal(got["hits.ids"], ref["hits.ids"])
+    assert not util.bit_mismatch(got["hits.f"], ref["hits.f"]).any()
+
+
 @pytest.mark.parametrize("scene", ["mixed", "sdf_small"])
 def test_first_hits_on_host_match_golden(vpt, hostsim, tmp_path, scene):
     rays = util.camera_rays(0, 0, np.random.default_rng(7), 4096)
@@ -116,19 +131,22 @@ def test_first_hits_on_host_match_golden(vpt, hostsim, tmp_path, scene):
         assert ref["hits.ids"][:, 0].sum() > 1000
 
 
-def test_instance_culling_never_hides_a_hit(vpt, hostsim, tmp_path):
+@pytest.mark.parametrize("scene,shader,spp,res,bounces,least", [("mixed", "volpathtrace", 2, 64, 8, 1000),
+                                                                ("skewed", "pathtrace", 2, 64, 4, 1000)])
+def test_instance_culling_never_hides_a_hit(vpt, hostsim, tmp_path, scene, shader, spp, res, bounces, least):
     """bvh.cuh skips an instance whose enlarged world box the ray misses (the reference transforms
     the ray and tests the root box in object space). `--cull-check` walks every culled instance the
-    way the reference would: none of them may hold a hit. The render must also stay the golden."""
+    way the reference would: none of them may hold a hit. The render must also stay the golden.
+    `skewed` holds frames with condition numbers up to ~750 (100 : 1 scales, shear): the margin
+    scales with the condition number (upload.cuh cull_record)."""
     import re
-    scene, shader, spp, res, bounces = "mixed", "volpathtrace", 2, 64, 8
     out = str(tmp_path / "h.vptarch")
     r = subprocess.run([hostsim, util.scene_path(scene), out, "--shader", shader, "--samples", str(spp),
                         "--resolution", str(res), "--bounces", str(bounces), "--cull-check"],
                        check=True, capture_output=True, text=True)
     m = re.search(r"cull check: (\d+) instances culled, (\d+) of them", r.stdout)
     assert m, r.stdout
-    assert int(m.group(1)) > 1000 and int(m.group(2)) == 0, r.stdout
+    assert int(m.group(1)) > least and int(m.group(2)) == 0, r.stdout
     got, ref = vpt.archive.load(out), golden(vpt, scene, shader, spp, res, bounces)
     assert not util.bit_mismatch(got["image_sum"], ref["image_sum"]).any()
     assert np.array_equal(got["rngs_after"], ref["rngs_after"])

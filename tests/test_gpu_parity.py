@@ -18,7 +18,7 @@ import util
 
 pytestmark = pytest.mark.gpu
 
-MESH_SCENES = ["03_volume", "01_surface", "mixed", "02_rollingteapot", "04_head1"]
+MESH_SCENES = ["03_volume", "01_surface", "mixed", "02_rollingteapot", "04_head1", "skewed"]
 SDF_SCENES = ["07_sdfunction", "06_gridsdf", "sdf_small"]
 
 

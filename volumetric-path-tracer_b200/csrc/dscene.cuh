@@ -72,7 +72,7 @@ struct DScene {
   // environments: 9 x f4 per env: frame(4) inverse rigid frame(4) {emission, tex}
   const f4* environments;
   int       num_environments;
-  // lights: 2 x i4 per light {instance, environment, sdf, cdf_off} {cdf_n,0,0,0}
+  // lights: 2 x i4 per light {instance, environment, sdf, cdf_off} {cdf_n, cdf sorted, 0, 0}
   const i4*    lights;
   const float* cdf;
   int          num_lights;

@@ -13,12 +13,29 @@
 
 namespace vpt {
 
-// sample_discrete: clamp then std::upper_bound (same bisection as libstdc++)
-VPT_FN int sample_discrete(const float* cdf, int n, float r) {
+// sample_discrete: clamp then std::upper_bound (same bisection as libstdc++).
+// `sorted` (lights record, set by the uploader / k_light_sorted when the running sums never
+// decrease): the upper bound of a sorted array does not depend on the probe order, so the
+// device first narrows the range 16-fold per step with 15 INDEPENDENT loads (one memory
+// latency per step instead of four; ncu r02c: the bisection's 17 dependent loads over the
+// 131 k-texel environment CDF were 12 % of k_wf_shade's stall samples at 5 lanes), then bisects.
+// An array that is not sorted keeps the reference's probe sequence.
+VPT_FN int sample_discrete(const float* cdf, int n, float r, bool sorted = false) {
   auto last = ld1(cdf + n - 1);
   r         = vclamp(r * last, (float)0, last - (float)0.00001);
   int first = 0, len = n;
   VPT_GUARD_DECL(guard);
+#if defined(__CUDA_ARCH__)
+  while (sorted && len > 32) {
+    int step = len >> 4;  // >= 2; pivots p_k = first + k step, k = 1 .. 15
+    int c    = 0;         // pivots with cdf[p_k] <= r: exactly p_1 .. p_c
+#pragma unroll
+    for (int k = 1; k < 16; k++) c += r < ld1(cdf + first + k * step) ? 0 : 1;
+    int lo = c > 0 ? first + c * step + 1 : first;
+    int hi = c < 15 ? first + (c + 1) * step : first + len;  // the bound is in [lo, hi]
+    first = lo, len = hi - lo;
+  }
+#endif
   while (len > 0) {
     VPT_GUARD_STEP(4, guard, 64);
     auto half = len >> 1;
@@ -48,7 +65,7 @@ VPT_CALL f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2
   auto l0 = ld4(sc.lights + 2 * light_id), l1 = ld4(sc.lights + 2 * light_id + 1);
   if (l0.x != invalidid) {
     auto in      = ld_instance(sc, l0.x);
-    auto element = sample_discrete(sc.cdf + l0.w, l1.x, rel);
+    auto element = sample_discrete(sc.cdf + l0.w, l1.x, rel, l1.y != 0);
     auto uv      = ruv;
     if (in.s.kind == kind_triangles) {
       auto sq = vsqrt(ruv.x);
@@ -67,7 +84,7 @@ VPT_CALL f3 sample_lights(const DScene& sc, f3 position, float rl, float rel, f2
     auto em = ld4(e + 8);
     if (f2i(em.w) != invalidid) {
       auto tex = ld4(sc.textures + f2i(em.w));
-      auto idx = sample_discrete(sc.cdf + l0.w, l1.x, rel);
+      auto idx = sample_discrete(sc.cdf + l0.w, l1.x, rel, l1.y != 0);
       auto uv  = f2{((idx % tex.x) + 0.5f) / tex.x, ((idx / tex.x) + 0.5f) / tex.y};
       return transform_direction(ld_frame(e),
           f3{vcos(uv.x * 2 * pif) * vsin(uv.y * pif), vcos(uv.y * pif),

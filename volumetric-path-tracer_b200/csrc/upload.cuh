@@ -383,8 +383,8 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     inst_frame.push_back(pack(frame.o, 0));
   }
   // world box of an instance for culling (bvh.cuh): the 8 transformed corners of the shape's
-  // root box, enlarged by 1e-4 of (extent + |coordinates|); valid for ray origins up to 100x
-  // that scale. Anything non-finite or empty disables culling for the instance.
+  // root box, enlarged by 1e-4 * cond(frame) of (extent + |coordinates|); valid for ray origins
+  // up to 100x that scale. Anything non-finite or empty disables culling for the instance.
   auto cull_record = [&](int i, f4& b0, f4& b1) {
     auto& inst = in.instances[i];
     b0 = {0, 0, 0, 0}, b1 = {0, 0, i2f(i), -1.0f};
@@ -409,7 +409,21 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
       scale    = s > scale ? s : scale;
     }
     if (!(scale > 0)) return;
-    double margin = 1e-4 * scale;
+    // The reference tests the ray in object space, where its rounding error grows with the
+    // condition number of the frame's linear part (eps * cond * |o|): the margin scales with
+    // cond (Frobenius bound, 1 for a rigid frame), and a frame beyond 1e3 is never culled.
+    double m[9], inv[9], f2 = 0, i2 = 0;
+    for (int k = 0; k < 9; k++) m[k] = inst.frame[k], f2 += m[k] * m[k];
+    double det = m[0] * (m[4] * m[8] - m[5] * m[7]) - m[3] * (m[1] * m[8] - m[2] * m[7]) +
+                 m[6] * (m[1] * m[5] - m[2] * m[4]);
+    if (!(std::fabs(det) > 0) || !(f2 < 1e300)) return;
+    inv[0] = m[4] * m[8] - m[5] * m[7], inv[1] = m[2] * m[7] - m[1] * m[8], inv[2] = m[1] * m[5] - m[2] * m[4];
+    inv[3] = m[5] * m[6] - m[3] * m[8], inv[4] = m[0] * m[8] - m[2] * m[6], inv[5] = m[2] * m[3] - m[0] * m[5];
+    inv[6] = m[3] * m[7] - m[4] * m[6], inv[7] = m[1] * m[6] - m[0] * m[7], inv[8] = m[0] * m[4] - m[1] * m[3];
+    for (int k = 0; k < 9; k++) i2 += (inv[k] / det) * (inv[k] / det);
+    double cond = std::sqrt(f2 * i2) / 3;
+    if (!(cond < 1e3)) return;
+    double margin = 1e-4 * scale * (cond > 1 ? cond : 1);
     b0 = {(float)(wmin[0] - margin), (float)(wmin[1] - margin), (float)(wmin[2] - margin),
         (float)(wmax[0] + margin)};
     b1 = {(float)(wmax[1] + margin), (float)(wmax[2] + margin), i2f(i), (float)(100 * scale)};
@@ -533,7 +547,11 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
         lt.sdf >= in.num_sdfs)
       return fail(VPT_ERR_INVALID, "light " + std::to_string(l) + " references a missing object");
     lights.push_back({lt.instance, lt.environment, lt.sdf, (int)cdf.size()});
-    lights.push_back({lt.num_elements, 0, 0, 0});
+    // .y: the running sums never decrease (lights.cuh sample_discrete may then probe in any order)
+    int sorted = lt.num_elements > 0 && lt.elements_cdf ? 1 : 0;
+    for (int k = 1; sorted && k < lt.num_elements; k++)
+      if (!(lt.elements_cdf[k] >= lt.elements_cdf[k - 1])) sorted = 0;
+    lights.push_back({lt.num_elements, sorted, 0, 0});
     // a null pointer reserves the range: vpt_cuda_upload_scene_device_lights fills it on the device
     if (lt.num_elements > 0 && lt.elements_cdf)
       cdf.insert(cdf.end(), lt.elements_cdf, lt.elements_cdf + lt.num_elements);

@@ -384,6 +384,18 @@ __global__ void __launch_bounds__(256) k_light_scan(const DScene sc, float* __re
   }
 }
 
+// the "running sums never decrease" flag of every light's CDF (lights record .y, see
+// lights.cuh sample_discrete): one block per light
+__global__ void __launch_bounds__(256) k_light_sorted(const DScene sc, i4* __restrict__ lights) {
+  int  l  = blockIdx.x;
+  auto l0 = ld4(sc.lights + 2 * l), l1 = ld4(sc.lights + 2 * l + 1);
+  int  ok = 1;
+  for (int k = 1 + threadIdx.x; k < l1.x; k += blockDim.x)
+    if (!(sc.cdf[l0.w + k] >= sc.cdf[l0.w + k - 1])) ok = 0;
+  ok = __syncthreads_and(ok);
+  if (threadIdx.x == 0) lights[2 * l + 1].y = ok && l1.x > 0 ? 1 : 0;
+}
+
 int vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** out,
     vpt_lights_stats* stats) {
   if (!desc || !out) return set_error(VPT_ERR_INVALID, "null argument");
@@ -443,6 +455,7 @@ int vpt_cuda_upload_scene_device_lights(const vpt_scene_desc* desc, vpt_scene** 
   }
   cudaEventRecord(e1);
   if (!lights.empty()) k_light_scan<<<(int)lights.size(), 256>>>(sc, cdf);
+  if (!lights.empty()) k_light_sorted<<<(int)lights.size(), 256>>>(sc, const_cast<i4*>(sc.lights));
   cudaEventRecord(e2);
   auto e = cudaEventSynchronize(e2);
   if (e == cudaSuccess) e = cudaGetLastError();
