@@ -1,8 +1,8 @@
 """Summarise an ncu --csv launch list (gpu__time_duration.sum [+ lane/instruction metrics]) per kernel
 and per wavefront iteration. usage: launch_summary.py launches.csv [every]"""
-import csv, sys, collections
+import csv, gzip, sys, collections
 
-rows = list(csv.reader(open(sys.argv[1])))
+rows = list(csv.reader(gzip.open(sys.argv[1], "rt") if sys.argv[1].endswith(".gz") else open(sys.argv[1])))
 every = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 start = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
 hdr = rows[start]
