@@ -59,7 +59,7 @@ constexpr int wf_block   = 128;
 constexpr int wf_pipes   = VPT_WF_PIPES;        // independent wavefronts (streams) per render call
 constexpr int wf_pipes_min_slots = 1 << 16;  // smaller images run one pipe
 constexpr int wf_batch   = 8;  // iterations enqueued between two looks at the counters
-constexpr int wf_timed_every = 4;  // with graphs: every 4th batch of pipe 0 carries the timed extend
+constexpr int wf_timed_every = 8;  // with graphs: every 8th batch of pipe 0 carries the timed extend
 constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped), last: suspended
 constexpr int wf_class_susp = wf_classes - 1;
 
