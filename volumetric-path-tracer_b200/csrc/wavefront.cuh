@@ -70,6 +70,7 @@ struct wf_counters {
   unsigned long long rays_extend, rays_lightpdf, paths_done;
   int                class_count[wf_classes];
   int                ext_head;  // next unclaimed entry of the extend queue (persistent extend)
+  int                pdf_head, pad2;  // next unclaimed entry of the light-pdf queue (persistent light pdf)
   int                count_shade;    // entries of the class-sorted queue that k_wf_shade runs
   int                susp_count[2];  // suspended-ray records in use, per pool
   unsigned long long rays_resumed;   // queue entries that were continuations, not new rays
@@ -998,6 +999,7 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
   if (blockIdx.x == 0 && threadIdx.x < wf_classes) w.counters->class_count[threadIdx.x] = 0;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     w.counters->ext_head = 0;
+    w.counters->pdf_head = 0;
     w.counters->susp_count[cur] = 0;  // that pool was consumed by this iteration's extend
   }
   if (tid < count) {
@@ -1052,6 +1054,136 @@ __global__ void __launch_bounds__(wf_block, VPT_PDF_BLOCKS)
   auto lpdf = sample_lights_pdf(sc, f3{a0.x, a0.y, a0.z}, f3{a0.w, a1.x, a1.y},
       prm.spheretrace_maxiter, st);
   w.at(wf_hit1, slot).z = lpdf;
+}
+
+// Persistent form of k_wf_lightpdf, same scheme as k_wf_extend_persistent: the grid is one
+// resident set of warps, a warp claims queue entries for its idle lanes, and sample_lights_pdf
+// (lights.cuh) runs as a per-lane state machine in rounds - `advance` walks the light list and
+// sums the closed-form terms (environment pdf) until a light needs an instance-targeted walk
+// or a single-field march, `walk` runs one trav_t::round of the current walk (up to 100 chained
+// walks per mesh light), `march` a few sphere-tracing steps - so that a lane whose query is over
+// takes the next queue entry instead of idling until the longest query of its warp ends
+// (ncu r02g: the one-thread-per-ray kernel ran 13 of 32 lanes on 03_volume, 10.8 on
+// 07_sdfunction). Per ray the arithmetic and its order are those of sample_lights_pdf.
+constexpr int wf_pdf_march_steps = 8;
+#if !defined(VPT_PDFP_BLOCKS)
+#define VPT_PDFP_BLOCKS VPT_PDF_BLOCKS
+#endif
+template <int S>
+__global__ void __launch_bounds__(wf_block, VPT_PDFP_BLOCKS)
+    k_wf_lightpdf_persistent(const DScene sc, const DParams prm, wf_view w, int cur) {
+  extern __shared__ int stack_mem[];
+  constexpr bool sdf  = is_sdf_shader<S>();
+  const unsigned full = 0xffffffffu;
+  const int      count = w.counters->count_pdf;
+  const int      lane  = threadIdx.x & 31;
+  stack_t st{stack_mem + vpt_stack_words * threadIdx.x, (int)blockDim.x};
+  if (blockIdx.x == 0 && threadIdx.x == 0) w.counters->rays_lightpdf += (unsigned long long)count;
+  enum : int { advance = 0, walk = 1, march = 2 };
+  bool   has = false, more = count > 0, running = true;
+  int    slot = 0, li = 0, bounce = 0, phase = advance, target = 0, mi = 0;
+  float  pdf = 0, lpdf = 0, area = 0, mt = 0;
+  f3     position{0, 0, 0}, direction{0, 0, 1}, next_position{0, 0, 0};
+  trav_t t;
+  t.cur = 0;
+  while (running) {
+    unsigned idle = __ballot_sync(full, !has);
+    if (more && __popc(idle) >= (sdf ? wf_refill_sdf : wf_refill)) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&w.counters->pdf_head, __popc(idle));
+      base = __shfl_sync(full, base, 0);
+      more = base + __popc(idle) < count;
+      int mine = base + __popc(idle & ((1u << lane) - 1));
+      if (!has && mine < count) {
+        slot    = w.queue_pdf[mine];
+        // after shade_hit the next ray is (position, incoming): the pdf is taken along it
+        auto a0 = w.at(wf_ray0, slot), a1 = w.at(wf_ray1, slot);
+        position = {a0.x, a0.y, a0.z}, direction = {a0.w, a1.x, a1.y};
+        pdf = 0, li = 0, phase = advance, has = true;
+      }
+    }
+    if (has && phase == advance) {
+      while (li < sc.num_lights && phase == advance) {
+        auto l0 = ld4(sc.lights + 2 * li), l1 = ld4(sc.lights + 2 * li + 1);
+        if (l0.x != invalidid) {
+          area = ld1(sc.cdf + l0.w + l1.x - 1);
+          lpdf = 0, next_position = position, bounce = 0, target = l0.x;
+          t.begin(sc, target, make_ray(next_position, direction), st);
+          phase = walk;
+        } else if (l0.z != invalidid) {
+          area = ld1(sc.cdf + l0.w + l1.x - 1);
+          target = l0.z, mt = 1e-4f, mi = 0;  // make_ray's tmin
+          phase  = march;
+        } else {
+          if (l0.y != invalidid) {
+            auto e  = sc.environments + 9 * l0.y;
+            auto em = ld4(e + 8);
+            if (f2i(em.w) != invalidid) {
+              auto tex      = ld4(sc.textures + f2i(em.w));
+              auto wl       = transform_direction(ld_frame(e + 4), direction);
+              auto texcoord = environment_texcoord(wl);
+              auto i    = vclamp((int)(texcoord.x * tex.x), 0, tex.x - 1);
+              auto j    = vclamp((int)(texcoord.y * tex.y), 0, tex.y - 1);
+              auto prob = sample_discrete_pdf(sc.cdf + l0.w, j * tex.x + i) / ld1(sc.cdf + l0.w + l1.x - 1);
+              auto angle = (2 * pif / tex.x) * (pif / tex.y) * vsin(pif * (j + 0.5f) / tex.y);
+              pdf += prob / angle;
+            } else {
+              pdf += 1 / (4 * pif);
+            }
+          }
+          li++;
+        }
+      }
+    }
+    if (has && phase == walk) {
+      auto ray = make_ray(next_position, direction);
+      if (!t.done()) t.round(sc, ray, st);
+      if (t.done()) {
+        if (t.h.hit) {
+          auto in        = ld_instance(sc, target);
+          auto lposition = eval_position(sc, in, t.h.element, t.h.uv);
+          auto lnormal   = eval_element_normal(sc, in, t.h.element);
+          lpdf += distance_squared(lposition, position) / (vabs(dot(lnormal, direction)) * area);
+          next_position = lposition + direction * 1e-3f;
+          bounce++;
+        }
+        if (!t.h.hit || bounce == 100) {
+          pdf += lpdf;
+          li++, phase = advance;
+        } else {
+          t.begin(sc, target, make_ray(next_position, direction), st);
+        }
+      }
+    }
+    if (has && phase == march) {
+      auto ray = make_ray(position, direction);
+      auto s   = ld_sdf(sc, target);
+      bool fin = false, hit = false;
+      for (int k = 0; k < wf_pdf_march_steps && !fin; k++) {
+        if (mi < prm.spheretrace_maxiter && mt < ray.tmax) {
+          auto res = eval_sdf_fn(s, transform_point(s.frame, ray_point(ray, mt)));
+          if (vabs(res) < (flt_eps * mt)) hit = true, fin = true;
+          else mt += res, ++mi;
+        } else {
+          fin = true;
+        }
+      }
+      if (fin) {
+        if (hit) {
+          auto lposition = ray_point(ray, mt);
+          // the reference evaluates the normal at the shading position (quirk kept)
+          auto lnormal = eval_sdf_normal_fn(s, position, mt);
+          pdf += distance_squared(lposition, position) / (vabs(dot(lnormal, direction)) * area);
+        }
+        li++, phase = advance;
+      }
+    }
+    if (has && phase == advance && li >= sc.num_lights) {
+      w.at(wf_hit1, slot).z = sc.num_lights > 0 ? pdf * ((float)1 / (float)sc.num_lights) : 0.0f;
+      has = false;
+    }
+    running = more || __any_sync(full, has);
+  }
 }
 
 template <int S>
@@ -1287,6 +1419,26 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       if (e != cudaSuccess) return e;
     }
   }
+  // persistent light pdf: opt-in (VPT_WF_PDF_PERSISTENT=1). Measured on B200, bit-identical and
+  // slower than one thread per queued ray on every scene (03_volume 181.3 vs 170.6 ms per 64 spp,
+  // 07_sdfunction 140.5 vs 136.5 ms per 16 spp; 96 / 128 registers: 177.6 / 180.5 ms): the state
+  // machine's bookkeeping and spills cost more than the refilled lanes give back
+  int pdf_resident = 0;
+  {
+    const char* pp_env = getenv("VPT_WF_PDF_PERSISTENT");  // read per call (tests run both kernels)
+    if (persistent && pp_env && atoi(pp_env) != 0) {
+      int per_sm = 0, device = 0, sms = 0;
+      cudaGetDevice(&device);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+      if (smem > 48 * 1024) {
+        e = cudaFuncSetAttribute(k_wf_lightpdf_persistent<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+      }
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_lightpdf_persistent<S>, wf_block, smem);
+      if (e != cudaSuccess) return e;
+      pdf_resident = per_sm * sms;
+    }
+  }
   // lanes still walking at or below which a warp parks its rays once the queue is empty
   const char* susp_env = getenv("VPT_WF_SUSPEND");  // read per call (tests sweep it)
   int suspend_at = susp_env ? atoi(susp_env) : wf_suspend;
@@ -1341,7 +1493,11 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     if (trace) trace->mark(grid);
     k_wf_shade<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
     if (trace) trace->mark(grid);
-    k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+    if (pdf_resident > 0)
+      k_wf_lightpdf_persistent<S><<<grid < pdf_resident ? grid : pdf_resident, wf_block, smem, p.stream>>>(
+          scene.d, prm, w, p.cur);
+    else
+      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
     k_wf_pdf_tail<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
     if (trace) trace->mark(grid);
     p.cur ^= 1;
@@ -1371,7 +1527,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     key.d = scene.d, key.prm = prm, key.view = p.view, key.image = image, key.rngs = rngs;
     key.suspend_at = pooled ? pool_limit : suspend_at, key.resident = pooled ? pool_resident : resident;
     key.grid = full, key.shader = S;
-    key.persistent = (persistent ? 1 : 0) | (pooled ? 2 : 0), key.smem = pooled ? pool_smem : smem;
+    key.persistent = (persistent ? 1 : 0) | (pooled ? 2 : 0) | (pdf_resident << 2), key.smem = pooled ? pool_smem : smem;
     auto& exec = p.graph[cls];
     auto& kept = p.graph_key[cls];
     if (exec && kept.size() == sizeof(key) && !memcmp(kept.data(), &key, sizeof(key))) return exec;
