@@ -9,7 +9,8 @@ b = e.load_package().binding
 b.set_device(0)
 cases = [("03_volume", "volpathtrace", 1280, 64, 64), ("01_surface", "pathtrace", 720, 4, 64),
          ("05_head1ss", "volpathtrace", 1280, 64, 64), ("02_rollingteapot", "pathtrace", 720, 4, 64),
-         ("07_sdfunction", "implicit", 1920, 4, 16), ("06_gridsdf", "implicit", 1280, 4, 16)]
+         ("07_sdfunction", "implicit", 1920, 4, 16), ("06_gridsdf", "implicit", 1280, 4, 16),
+         ("04_head1", "volpathtrace", 1280, 64, 16)]
 VAR = os.environ.get("AB_VAR", "VPT_WF_POOL")
 only = sys.argv[1:]
 for scene, shader, res, bounces, spp in cases:

@@ -1375,7 +1375,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     resident = per_sm * sms;
     // VPT_WF_EXT_BLOCKS=<n>: resident extend blocks per SM (experiments: leaves room for the
     // other pipe's kernels next to a running extend)
-    static const char* blocks_env = getenv("VPT_WF_EXT_BLOCKS");
+    const char* blocks_env = getenv("VPT_WF_EXT_BLOCKS");  // read per call
     if (blocks_env && atoi(blocks_env) > 0 && atoi(blocks_env) < per_sm) resident = atoi(blocks_env) * sms;
     if (resident <= 0) persistent = false;
   }
