@@ -59,3 +59,18 @@ def test_persistent_light_pdf_is_bit_identical(vpt, monkeypatch, scene, shader, 
     assert not util.bit_mismatch(got, want).any()
     assert np.array_equal(got_rng, want_rng)
     assert np.abs(want).sum() > 0
+
+
+@pytest.mark.parametrize("scene,shader,res,bounces", [("mixed", "volpathtrace", 128, 16), ("01_surface", "pathtrace", 256, 4)])
+def test_extend_register_builds_are_bit_identical(vpt, monkeypatch, scene, shader, res, bounces):
+    """VPT_WF_ROOMY=0 / 1: k_wf_extend_persistent compiled for 6 blocks per SM (80 registers) and for 5
+    (96 registers); the host picks by the scene's triangle count, the image cannot depend on it."""
+    path = util.scene_path(scene)
+    if path is None:
+        pytest.skip(f"{scene} not built")
+    monkeypatch.setenv("VPT_WF_ROOMY", "0")
+    want, want_rng = render(vpt, path, shader, res, bounces, 5)
+    monkeypatch.setenv("VPT_WF_ROOMY", "1")
+    got, got_rng = render(vpt, path, shader, res, bounces, 5)
+    assert not util.bit_mismatch(got, want).any()
+    assert np.array_equal(got_rng, want_rng)

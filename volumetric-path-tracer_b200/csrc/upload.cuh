@@ -95,6 +95,7 @@ struct flat_scene {
   DScene      d{};
   device_pool pool;
   int         stack_depth = 1;  // traversal stack entries a thread can need
+  long long   num_triangles = 0;  // triangle primitives over all shapes (picks the extend build, wavefront.cuh)
   int         num_cameras = 0;
   std::vector<float> camera_aspect;
 };
@@ -340,6 +341,7 @@ inline int flatten_scene(const vpt_scene_desc& in, flat_scene& out, std::string&
     max_shape_depth = depth > max_shape_depth ? depth : max_shape_depth;
     int stride    = kind == kind_triangles ? 3 : 4;
     int prim_base = (int)prims.size();
+    if (kind == kind_triangles) out.num_triangles += bvh.num_primitives;
     for (int k = 0; k < bvh.num_primitives; k++) {
       int e = bvh.primitives[k];
       if (e < 0 || e >= nelem)

@@ -517,8 +517,15 @@ constexpr int wf_suspend   = VPT_WF_SUSPEND_AT;  // 0: never park (drain in plac
 #endif
 constexpr int wf_sdf_steps = VPT_WF_SDF_STEPS;
 
-template <int S>
-__global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS)
+// ROOMY = 1: the same kernel compiled for one resident block fewer per SM (96 instead of 80
+// registers). Measured on B200: triangle meshes walk faster with the registers (05_head1ss
+// 203.1 -> 193.9 ms per 64 spp, 04_head1 33.0 -> 31.4, 01_surface 52.2 -> 50.7), the all-quad
+// 03_volume and sphere tracing with the residency (170.9 vs 172.4, 135.5 vs 140.2 ms); running
+// the 80-register build at fewer blocks changes nothing, so it is the registers. The host picks
+// by the scene's triangle count (wf_roomy_triangles); results do not depend on the choice.
+constexpr long long wf_roomy_triangles = 2048;
+template <int S, int ROOMY>
+__global__ void __launch_bounds__(wf_block, VPT_EXT_BLOCKS - ROOMY)
     k_wf_extend_persistent(const DScene sc, const DParams prm, wf_view w, int cur, int suspend_at) {
   extern __shared__ int stack_mem[];
 #if defined(VPT_WF_COOP_LEAVES)
@@ -1350,11 +1357,18 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   auto e = wf.reserve(slots, npipes);
   if (e != cudaSuccess) return e;
   size_t smem = (size_t)scene.stack_depth * vpt_stack_words * wf_block * sizeof(int);
+  // the extend build: see k_wf_extend_persistent (VPT_WF_ROOMY=0 / 1 overrides the scene rule)
+  auto ext_kernel = k_wf_extend_persistent<S, 0>;
+  int  roomy      = 0;
+  if constexpr (!is_sdf_shader<S>()) {
+    const char* roomy_env = getenv("VPT_WF_ROOMY");  // read per call
+    roomy = roomy_env ? (atoi(roomy_env) != 0) : scene.num_triangles >= wf_roomy_triangles;
+    if (roomy) ext_kernel = k_wf_extend_persistent<S, 1>;
+  }
   if (smem > 48 * 1024) {
     e = cudaFuncSetAttribute(k_wf_extend<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(k_wf_extend_persistent<S>,
-          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      e = cudaFuncSetAttribute(ext_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(k_wf_lightpdf<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
           (int)smem);
@@ -1369,8 +1383,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     int per_sm = 0, device = 0, sms = 0;
     cudaGetDevice(&device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend_persistent<S>, wf_block,
-        smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ext_kernel, wf_block, smem);
     if (e != cudaSuccess) return e;
     resident = per_sm * sms;
     // VPT_WF_EXT_BLOCKS=<n>: resident extend blocks per SM (experiments: leaves room for the
@@ -1484,8 +1497,8 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       k_wf_extend_pool<S><<<blocks < pool_resident ? blocks : pool_resident, wf_block, pool_smem, p.stream>>>(
           scene.d, prm, w, p.cur, pool_limit);
     } else if (persistent)
-      k_wf_extend_persistent<S><<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(
-          scene.d, prm, w, p.cur, suspend_at);
+      ext_kernel<<<grid < resident ? grid : resident, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur,
+          suspend_at);
     else
       k_wf_extend<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
     if (timed) cudaEventRecord(wf.k1, p.stream);
@@ -1527,7 +1540,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
     key.d = scene.d, key.prm = prm, key.view = p.view, key.image = image, key.rngs = rngs;
     key.suspend_at = pooled ? pool_limit : suspend_at, key.resident = pooled ? pool_resident : resident;
     key.grid = full, key.shader = S;
-    key.persistent = (persistent ? 1 : 0) | (pooled ? 2 : 0) | (pdf_resident << 2), key.smem = pooled ? pool_smem : smem;
+    key.persistent = (persistent ? 1 : 0) | (pooled ? 2 : 0) | (roomy ? 4 : 0) | (pdf_resident << 3), key.smem = pooled ? pool_smem : smem;
     auto& exec = p.graph[cls];
     auto& kept = p.graph_key[cls];
     if (exec && kept.size() == sizeof(key) && !memcmp(kept.data(), &key, sizeof(key))) return exec;
