@@ -1046,8 +1046,10 @@ __global__ void __launch_bounds__(wf_block, VPT_SHADE_BLOCKS)
 #if !defined(VPT_PDF_BLOCKS)
 #define VPT_PDF_BLOCKS 6
 #endif
-template <int S>
-__global__ void __launch_bounds__(wf_block, VPT_PDF_BLOCKS)
+// ROOMY: as for k_wf_extend_persistent (96 instead of 80 registers; the instance walks of a
+// triangle-mesh light gain the same way: 04_head1 837 -> 870, 02_rollingteapot 346 -> 353 Mpaths/s)
+template <int S, int ROOMY>
+__global__ void __launch_bounds__(wf_block, VPT_PDF_BLOCKS - ROOMY)
     k_wf_lightpdf(const DScene sc, const DParams prm, wf_view w, int cur) {
   extern __shared__ int stack_mem[];
   int tid   = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1359,19 +1361,19 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   size_t smem = (size_t)scene.stack_depth * vpt_stack_words * wf_block * sizeof(int);
   // the extend build: see k_wf_extend_persistent (VPT_WF_ROOMY=0 / 1 overrides the scene rule)
   auto ext_kernel = k_wf_extend_persistent<S, 0>;
+  auto pdf_kernel = k_wf_lightpdf<S, 0>;
   int  roomy      = 0;
   if constexpr (!is_sdf_shader<S>()) {
     const char* roomy_env = getenv("VPT_WF_ROOMY");  // read per call
     roomy = roomy_env ? (atoi(roomy_env) != 0) : scene.num_triangles >= wf_roomy_triangles;
-    if (roomy) ext_kernel = k_wf_extend_persistent<S, 1>;
+    if (roomy) ext_kernel = k_wf_extend_persistent<S, 1>, pdf_kernel = k_wf_lightpdf<S, 1>;
   }
   if (smem > 48 * 1024) {
     e = cudaFuncSetAttribute(k_wf_extend<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(ext_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(k_wf_lightpdf<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-          (int)smem);
+      e = cudaFuncSetAttribute(pdf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(k_wf_drain<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -1510,7 +1512,7 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
       k_wf_lightpdf_persistent<S><<<grid < pdf_resident ? grid : pdf_resident, wf_block, smem, p.stream>>>(
           scene.d, prm, w, p.cur);
     else
-      k_wf_lightpdf<S><<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
+      pdf_kernel<<<grid, wf_block, smem, p.stream>>>(scene.d, prm, w, p.cur);
     k_wf_pdf_tail<S><<<grid, wf_block, 0, p.stream>>>(scene.d, prm, w, image, rngs, p.cur);
     if (trace) trace->mark(grid);
     p.cur ^= 1;
