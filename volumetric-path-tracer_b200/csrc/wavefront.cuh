@@ -53,11 +53,9 @@
 namespace vpt {
 
 constexpr int wf_block   = 128;
-#if !defined(VPT_WF_PIPES)
-#define VPT_WF_PIPES 2
-#endif
-constexpr int wf_pipes   = VPT_WF_PIPES;        // independent wavefronts (streams) per render call
+// independent wavefronts (streams) per render call: 1 .. 3 by image size, see run_wavefront_shader
 constexpr int wf_pipes_min_slots = 1 << 16;  // smaller images run one pipe
+constexpr int wf_pipes_two_slots = 300000, wf_pipes_one_slots = 1200000;  // see run_wavefront_shader
 constexpr int wf_batch   = 8;  // iterations enqueued between two looks at the counters
 constexpr int wf_timed_every = 8;  // with graphs: every 8th batch of pipe 0 carries the timed extend
 constexpr int wf_classes = 64;  // 0 miss, 1 in-volume, 2.. material id (clamped), last: suspended
@@ -1352,8 +1350,13 @@ cudaError_t run_wavefront_shader(const flat_scene& scene, wavefront_buffers& wf,
   // pipes: VPT_WF_PIPES overrides; small images, traced runs and sphere tracing (whose extend
   // keeps the issue slots 88 % busy on its own: B200, 07_sdfunction 140 vs 136 Mpaths/s) use one
   const char* pipes_env = getenv("VPT_WF_PIPES");  // read per call: bench.py samples one pipe alone
+  // by image size (B200, 64 / 16 spp calls): a 1.5 M-pixel wavefront fills the machine on its own
+  // (05_head1ss 186.7 ms with one pipe, 194.6 with two; 03_volume at 1920x800 87.0 vs 89.0), around
+  // 0.2 M pixels a third pipe still hides latency (02_rollingteapot 37.4 vs 38.6 ms, 01_surface
+  // 49.7 vs 51.0), in between two (03_volume 1280x533: 171.0 ms with two, 177.9 / 175.4 with one / three)
+  int by_size = slots >= wf_pipes_one_slots ? 1 : (slots >= wf_pipes_two_slots ? 2 : 3);
   int npipes = pipes_env ? atoi(pipes_env)
-                         : (slots >= wf_pipes_min_slots && !is_sdf_shader<S>() ? wf_pipes : 1);
+                         : (slots >= wf_pipes_min_slots && !is_sdf_shader<S>() ? by_size : 1);
   npipes     = npipes < 1 ? 1 : (npipes > wf_max_pipes ? wf_max_pipes : npipes);
   if (trace) npipes = 1;
   auto e = wf.reserve(slots, npipes);
