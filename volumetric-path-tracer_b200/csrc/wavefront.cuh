@@ -120,7 +120,7 @@ struct wf_view {
 };
 
 // One pipe = an independent wavefront over an interleaved share of the slots (tile t belongs
-// to pipe t % pipes), with its own queues, counters and CUDA stream. Two pipes let the
+// to pipe t % pipes), with its own queues, counters and CUDA stream. Several pipes let the
 // latency-bound kernels of one (shade, light pdf, the draining end of extend) run in the issue
 // slots the other leaves idle; pixels do not interact, so results do not depend on the split.
 constexpr int wf_max_pipes = 4;
