@@ -170,16 +170,38 @@ class ClockSampler(threading.Thread):
         self.gpu, self.stop_flag, self.rows = gpu_index, threading.Event(), []
 
     def run(self):
+        # NVML in-process when the binding is here (a query costs microseconds); else the nvidia-smi
+        # binary. Spawning nvidia-smi five times a second from rank 0 delayed that rank by some
+        # 10 ms per step on an 8-GPU box, which the other ranks then waited for inside the reduce.
+        nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            handle = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            nvml = pynvml
+        except Exception:
+            nvml = None
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.QUERY}",
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if nvml is not None:
+                    sm = nvml.nvmlDeviceGetClockInfo(handle, nvml.NVML_CLOCK_SM)
+                    top = nvml.nvmlDeviceGetMaxClockInfo(handle, nvml.NVML_CLOCK_SM)
+                    try:
+                        bits = nvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+                    except Exception:
+                        bits = nvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
+                    flag = lambda mask: "Active" if bits & mask else "Not Active"
+                    # hw_slowdown 0x8, hw_thermal_slowdown 0x40, sw_thermal_slowdown 0x20, sw_power_cap 0x4
+                    self.rows.append([str(sm), str(top), flag(0x8), flag(0x40), flag(0x20), flag(0x4)])
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.QUERY}",
+                                          "--format=csv,noheader,nounits"], capture_output=True,
+                                         text=True, timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(0.1 if nvml is not None else 0.5)
 
     def summary(self):
         self.stop_flag.set()
@@ -301,6 +323,13 @@ class Bench:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return [float(v) for v in t.tolist()]
 
+    def gather_over_ranks(self, value):
+        t = self.torch.zeros(self.world, dtype=self.torch.float64, device="cuda")
+        t[self.rank] = value
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return [round(float(v), 3) for v in t.tolist()]
+
     def reduce_to_rank0(self, r, total_samples):
         """The one collective of the path: sum of the accumulation images on rank 0 (NCCL)."""
         if self.dist is None:
@@ -309,6 +338,9 @@ class Bench:
         acc = torch.empty(r.height * r.width * 4, dtype=torch.float32, device="cuda")
         r.export_image(acc.data_ptr())
         torch.cuda.synchronize()
+        # ranks enter the collective together: its device time is then the reduce itself, not the
+        # wait for a rank whose host thread fell behind between steps
+        self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         self.pkg.sharding.reduce_images(acc, dst=0)
@@ -387,6 +419,7 @@ def measure(bn, name, steps, warmup, full):
         img = r.image(normalized=True)
         image_mean = float(np.clip(img[..., :3], 0, 4).mean())
 
+    r.pin()  # page-locked host mirrors for the transfer loop below (outside the clock, like cudaMallocHost)
     # ---- end to end through the host API with host buffers -----------------------------------
     # per step: generators up from pinned host memory, trace, (N > 1: the NCCL reduce,) the
     # accumulation image down to the host
@@ -417,6 +450,7 @@ def measure(bn, name, steps, warmup, full):
     scene.close()
 
     worst_ms, worst_e2e_ms = bn.max_over_ranks([total_ms + reduce_ms, e2e_s * 1e3])
+    per_rank_ms = bn.gather_over_ranks(total_ms / steps)  # every rank's own device time per step
     value = bn.world * paths_per_step * steps / (worst_ms / 1e3) / 1e6
     e2e_value = bn.world * paths_per_step * e2e_steps / (worst_e2e_ms / 1e3) / 1e6
     ms_per_step = worst_ms / steps
@@ -426,6 +460,7 @@ def measure(bn, name, steps, warmup, full):
                 step_tflops=step_tflops, fpp=fpp, launches=launches, graphs=graphs, clocks=clocks,
                 top=(top_ms, top_units, top_launches), alone=alone, reduce_ms=reduce_ms,
                 image_mean=image_mean, host_build_s=host_build_s, upload_s=upload_s, pix=pix,
+                per_rank_ms=per_rank_ms,
                 size=(wl["size"][0], wl["size"][1]), paths_per_step=paths_per_step)
 
 
@@ -445,17 +480,25 @@ def strong_leg(bn, name, total_spp):
     bn.barrier()
     t0 = time.time()
     done = 0
+    calls = []
     while done < mine:
         n = min(64, mine - done)
+        tc = time.time()
         r.trace(n)  # the first call uploads the scene
+        calls.append(time.time() - tc)
         done += n
+    t_render = time.time() - t0
     bn.reduce_to_rank0(r, total_spp)
+    t_reduce = time.time() - t0 - t_render
     if bn.rank == 0:
         img = r.image(normalized=False)
         del img
     torch.cuda.synchronize()
     seconds = time.time() - t0
-    (worst,) = bn.max_over_ranks([seconds])
+    # where the clock goes on the slowest rank: first (cold) call, the other calls, reduce (includes
+    # waiting for the slowest rank), download
+    worst, first_call, other_calls, reduce_s = bn.max_over_ranks(
+        [seconds, calls[0], sum(calls[1:]), t_reduce])
     paths = wl["size"][0] * wl["size"][1] * total_spp
     r.close()
     scene.close()
@@ -463,6 +506,8 @@ def strong_leg(bn, name, total_spp):
                         f"{total_spp} spp in total",
             "n_gpus": bn.world, "spp_total": total_spp, "spp_this_rank": mine,
             "seconds": worst, "value": paths / worst / 1e6, "unit": "Mpaths/s", "scaling": "strong",
+            "breakdown_s": {"first_call": first_call, "other_calls": other_calls, "calls": len(calls),
+                            "reduce_and_wait": reduce_s, "download": max(0.0, seconds - t_render - t_reduce)},
             "clock": "scene upload + cold first call + render + NCCL reduce + one D2H of the sum; "
                      "max over ranks (wall clock around blocking calls)"}
 
@@ -533,6 +578,7 @@ def gpu_arm(args, wl, rank, world, local_rank):
                                          "graph launch"},
             "clocks": m["clocks"], "roofline": roofline_block(args.workload, m, wl),
             "reduce_ms": m["reduce_ms"], "image_mean": m["image_mean"],
+            "per_rank_ms_per_step": m["per_rank_ms"],
             "host_build_s": m["host_build_s"], "scene_upload_s": m["upload_s"],
         }
         if world == 1 and not args.no_cpu_baseline:

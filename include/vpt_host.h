@@ -59,6 +59,9 @@ int  vpth_render_size(const vpth_render* render, int32_t* width, int32_t* height
 int  vpth_render_get_rngs(vpth_render* render, uint64_t* rngs); /* [w*h][2], synced from the device */
 /* back to sample 0 with the make_state generators, advanced by rng_offset draws per pixel */
 int  vpth_render_reset(vpth_render* render, uint64_t rng_offset);
+/* page-lock the render's host mirrors now (otherwise: after its third host transfer). Worth it for
+ * loops that move the generators / the image every step; a render that downloads once skips it */
+int  vpth_render_pin(vpth_render* render);
 
 /* pathtrace_samples with a batch of nsamples; blocking */
 int  vpth_render_samples(vpth_render* render, int nsamples);

@@ -263,6 +263,10 @@ class Render:
         _check(self._host.vpth_render_get_rngs(self._h, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def pin(self):
+        """Page-lock the host mirrors now (default: after the third host transfer)."""
+        _check(self._host.vpth_render_pin(self._h))
+
     def reset(self, rng_offset: int = 0) -> None:
         _check(self._host.vpth_render_reset(self._h, C.c_uint64(rng_offset)))
 

@@ -1,6 +1,9 @@
 // vpt_host_c.cpp — extern "C" wrappers of the C++ facade (include/vpt_host.h),
 // used by the Python tests / bench through ctypes. Exceptions never cross the
 // C boundary: they become a negative status + vpth_last_error().
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/vpt_host.h"
@@ -21,6 +24,15 @@ struct vpth_render {
   pathtrace_state        state;
   std::vector<rng_state> initial_rngs;
   std::vector<void*>     pinned;
+  int                    transfers = 0;
+  // Page-locking the three host mirrors costs 60 - 230 ms (24 MB each at 1920x800; the calls of
+  // several processes serialise in the kernel: 8 ranks of one box paid 150 - 230 ms each) and
+  // saves about a millisecond per transfer, so it happens on request (vpth_render_pin) or once a
+  // render has moved its mirrors three times (a preview / end-to-end loop), not for a render
+  // that downloads one image at the end.
+  void note_transfer() {
+    if (++transfers >= 3) pin();
+  }
   // page-lock the host mirrors once a device exists (best effort)
   void pin() {
     if (!pinned.empty() || vpt_cuda_device_count() < 1) return;
@@ -272,19 +284,42 @@ int vpth_render_get_rngs(vpth_render* r, uint64_t* rngs) {
 
 int vpth_render_reset(vpth_render* r, uint64_t rng_offset) {
   if (!r) return VPT_ERR_INVALID;
-  return guarded([&] { reset_device_state(r->state, r->initial_rngs, rng_offset); });
+  return guarded([&] {
+    r->note_transfer();
+    reset_device_state(r->state, r->initial_rngs, rng_offset);
+  });
+}
+
+int vpth_render_pin(vpth_render* r) {
+  if (!r) return VPT_ERR_INVALID;
+  return guarded([&] { r->pin(); });
 }
 
 int vpth_render_samples(vpth_render* r, int nsamples) {
   if (!r || nsamples <= 0) return VPT_ERR_INVALID;
   return guarded([&] {
     auto s = r->owner;
+    // VPT_HOST_TRACE=1: wall-clock split of the call (scene upload / binding / trace)
+    static const bool trace = getenv("VPT_HOST_TRACE") != nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&] {
+      auto t1 = std::chrono::steady_clock::now();
+      auto ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+      t0 = t1;
+      return ms;
+    };
+    double ms_upload = 0, ms_bind = 0, ms_pin = 0;
     if (!s->device) s->device = upload_scene(s->scene, s->bvh, s->lights);
+    ms_upload = lap();
     bind_device_scene(r->state, s->device, s->scene, s->bvh, s->lights);
-    r->pin();
+    ms_bind = lap();
+    ms_pin = lap();
     auto params  = r->params;
     params.batch = nsamples;
     pathtrace_samples(r->state, s->scene, s->bvh, s->lights, params);
+    if (trace)
+      fprintf(stderr, "[vpt host] upload %.1f ms, bind %.1f ms, trace %.1f ms (%d samples)\n", ms_upload,
+          ms_bind + ms_pin, lap(), nsamples);
   });
 }
 
@@ -299,6 +334,7 @@ int vpth_render_done_samples(const vpth_render* r) { return r ? r->state.samples
 int vpth_render_get_image(vpth_render* r, float* rgba, int normalized) {
   if (!r || !rgba) return VPT_ERR_INVALID;
   return guarded([&] {
+    r->note_transfer();
     auto n = (size_t)r->state.width * r->state.height;
     if (normalized) {
       auto img = get_render(r->state);
