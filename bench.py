@@ -430,7 +430,7 @@ def measure(bn, name, steps, warmup, full):
         r.reset(bn.rng_offset)          # H2D
         r.trace(spp)
         bn.reduce_to_rank0(r, spp * bn.world)
-        host_img = r.image(normalized=False)  # D2H
+        host_img = r.image_view()  # D2H into the render's page-locked host image (pathtrace_state::image)
     torch.cuda.synchronize()
     e2e_s = time.time() - t0
     del host_img

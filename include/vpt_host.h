@@ -69,6 +69,10 @@ int  vpth_render_done_samples(const vpth_render* render);
 /* normalized != 0: get_render (sum / samples); else the raw sums */
 int  vpth_render_get_image(vpth_render* render, float* rgba, int normalized);
 /* device-side output stage: 8-bit sRGB RGBA of the current render, [height][width][4] */
+/* the un-normalised accumulation image WITHOUT a copy: brings pathtrace_state::image (the host mirror,
+ * page-locked once pinned) up to date and returns its address, [h][w][4] floats, valid until the next
+ * call on this render. What a reference caller gets by reading state.image */
+int  vpth_render_image_view(vpth_render* render, const float** rgba);
 int  vpth_render_get_srgb8(vpth_render* render, uint8_t* rgba);
 /* get_render + tonemap(exposure, filmic) + 8 bit on the device (vpt_cuda_download_tonemapped8) */
 int  vpth_render_get_tonemapped8(vpth_render* render, float exposure, int filmic, uint8_t* rgba);

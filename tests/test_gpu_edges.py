@@ -161,3 +161,22 @@ def test_parked_rays_never_change_the_image(vpt, monkeypatch, suspend):
                       bounces=4, pipeline="wavefront")
     assert not util.bit_mismatch(img, ref["image_sum"]).any()
     assert np.array_equal(rng, ref["rngs_after"])
+
+
+def test_image_view_is_the_image_without_a_copy(vpt):
+    """vpth_render_image_view: the host mirror itself (read-only numpy view), equal to image(False);
+    a second render call refreshes it in place."""
+    b = vpt.binding
+    sc = b.Scene(util.scene_path("mixed"))
+    r = b.Render(sc, b.make_params(shader="pathtrace", samples=16, resolution=64))
+    r.trace(2)
+    view = r.image_view()
+    assert view.shape == (r.height, r.width, 4) and not view.flags.writeable
+    assert not util.bit_mismatch(view, r.image(normalized=False)).any()
+    before = view.copy()
+    r.trace(2)
+    again = r.image_view()
+    assert again.ctypes.data == view.ctypes.data
+    assert util.bit_mismatch(again, before).any()
+    assert not util.bit_mismatch(again, r.image(normalized=False)).any()
+    r.close(), sc.close()

@@ -282,6 +282,15 @@ class Render:
         _check(self._host.vpth_render_get_image(self._h, _fptr(out), int(normalized)))
         return out
 
+    def image_view(self) -> np.ndarray:
+        """Un-normalised accumulation image [h, w, 4] as a read-only VIEW of the render's host mirror
+        (no copy, no allocation): valid until the next call on this render."""
+        ptr = C.POINTER(C.c_float)()
+        _check(self._host.vpth_render_image_view(self._h, C.byref(ptr)))
+        arr = np.ctypeslib.as_array(ptr, shape=(self.height, self.width, 4))
+        arr.flags.writeable = False
+        return arr
+
     def image_srgb8(self) -> np.ndarray:
         """Output stage on the device: get_render + rgb_to_srgb + float_to_byte -> [h, w, 4] uint8."""
         out = np.zeros((self.height, self.width, 4), dtype=np.uint8)

@@ -346,6 +346,15 @@ int vpth_render_get_image(vpth_render* r, float* rgba, int normalized) {
   });
 }
 
+int vpth_render_image_view(vpth_render* r, const float** rgba) {
+  if (!r || !rgba) return VPT_ERR_INVALID;
+  return guarded([&] {
+    r->note_transfer();
+    sync_image(r->state);
+    *rgba = (const float*)r->state.image.data();
+  });
+}
+
 int vpth_render_get_srgb8(vpth_render* r, uint8_t* rgba) {
   if (!r || !rgba) return VPT_ERR_INVALID;
   return guarded([&] {
