@@ -22,7 +22,7 @@ struct vpth_render {
   vpth_scene*            owner = nullptr;
   pathtrace_params       params;
   pathtrace_state        state;
-  std::vector<rng_state> initial_rngs;
+  std::shared_ptr<const std::vector<rng_state>> initial_rngs;
   std::vector<void*>     pinned;
   int                    transfers = 0;
   // Page-locking the three host mirrors costs 60 - 230 ms (24 MB each at 1920x800; the calls of
@@ -39,7 +39,7 @@ struct vpth_render {
     auto reg = [&](void* p, size_t n) {
       if (n && vpt_cuda_host_register(p, n) == VPT_OK) pinned.push_back(p);
     };
-    reg(initial_rngs.data(), initial_rngs.size() * sizeof(rng_state));
+    if (initial_rngs) reg((void*)initial_rngs->data(), initial_rngs->size() * sizeof(rng_state));
     reg(state.rngs.data(), state.rngs.size() * sizeof(rng_state));
     reg(state.image.data(), state.image.size() * sizeof(vec4f));
   }
@@ -256,7 +256,7 @@ int vpth_render_create(vpth_scene* scene, const vpt_params* params, vpth_render*
     r->owner        = scene;
     r->params       = from_c_params(*params);
     r->state        = make_state(scene->scene, r->params);
-    r->initial_rngs = r->state.rngs;
+    r->initial_rngs = std::make_shared<const std::vector<rng_state>>(r->state.rngs);
   });
   if (e != VPT_OK) {
     delete r;

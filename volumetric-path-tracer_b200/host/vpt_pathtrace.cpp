@@ -168,7 +168,7 @@ struct device_binding {
   std::vector<std::unique_ptr<device_replica>> replicas = {};
   int         root_device = 0;
   // what every GPU's generators derive from: base_rngs advanced by rng_offset (+ rank << 40)
-  std::vector<rng_state> base_rngs = {};
+  std::shared_ptr<const std::vector<rng_state>> base_rngs;
   uint64_t    rng_offset  = 0;
   vpt_state*  state     = nullptr;
   const void* scene_key = nullptr;
@@ -366,7 +366,8 @@ static device_binding& bind(pathtrace_state& state, const scene_data& scene,
     check(vpt_cuda_create_state(state.width, state.height, (const uint64_t*)state.rngs.data(),
               &dev.state),
         "vpt_cuda_create_state");
-    if (dev.base_rngs.empty()) dev.base_rngs = state.rngs, dev.rng_offset = 0;
+    if (!dev.base_rngs)
+      dev.base_rngs = std::make_shared<const std::vector<rng_state>>(state.rngs), dev.rng_offset = 0;
   }
   return dev;
 }
@@ -402,7 +403,7 @@ static void bind_replicas(device_binding& dev, pathtrace_state& state, const sce
       if (!ok(vpt_cuda_set_device(rep.device))) return;
       if (!ok(vpt_cuda_upload_scene(&storage.desc, &rep.scene))) return;
       if (!ok(vpt_cuda_create_state(state.width, state.height,
-              (const uint64_t*)dev.base_rngs.data(), &rep.state)))
+              (const uint64_t*)dev.base_rngs->data(), &rep.state)))
         return;
       ok(vpt_cuda_advance_rngs(rep.state, dev.rng_offset + rank_rng_offset(r)));
     });
@@ -503,9 +504,17 @@ void sync_state(pathtrace_state& state) {
 
 void reset_device_state(pathtrace_state& state, const std::vector<rng_state>& rngs,
     uint64_t rng_offset) {
+  reset_device_state(state, std::make_shared<const std::vector<rng_state>>(rngs), rng_offset);
+}
+
+// the caller shares ownership of the generators: no 16-bytes-per-pixel copy per restart
+void reset_device_state(pathtrace_state& state,
+    const std::shared_ptr<const std::vector<rng_state>>& shared_rngs, uint64_t rng_offset) {
+  if (!shared_rngs) throw std::invalid_argument("reset_device_state: null generators");
   if (!state.device) state.device = std::make_shared<device_binding>();
   auto& dev     = *state.device;
-  dev.base_rngs = rngs;
+  auto& rngs    = *shared_rngs;
+  dev.base_rngs = shared_rngs;
   if (!dev.state) {
     // no device state yet: restart the host copies (same O(log n) PCG32 jump as the device's)
     state.rngs = rngs;

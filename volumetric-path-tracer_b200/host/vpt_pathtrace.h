@@ -199,6 +199,8 @@ void mark_host_stale(pathtrace_state& state);
 // mirrors are refreshed on the next sync. Before the first sample the host copies are restarted.
 void reset_device_state(pathtrace_state& state, const std::vector<rng_state>& rngs,
     uint64_t rng_offset);
+void reset_device_state(pathtrace_state& state,
+    const std::shared_ptr<const std::vector<rng_state>>& rngs, uint64_t rng_offset = 0);
 
 // Device statistics of the last pathtrace_samples call on this state.
 vpt_trace_stats get_trace_stats(const pathtrace_state& state);
